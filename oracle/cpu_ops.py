@@ -1,0 +1,136 @@
+"""ctypes wrappers around oracle/libgnd_oracle.so (TEST INFRASTRUCTURE ONLY).
+
+The functions keep the reference's Python signatures so the parity tests read
+like calls into the reference:
+
+  points_to_voxel        utils/point_cloud_ops.py:107-167
+  shift_cloud            predict_ground.py:104-107 (_shift_cloud)
+  segment_cloud          utils/utils.py:198-220
+  segment_cloud_noground utils/utils.py:222-248
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libgnd_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    """Compile the C restatement (gcc); called by __graft_entry__.build()."""
+    src = os.path.join(_HERE, "gnd_oracle.c")
+    if (not force and os.path.exists(_LIB_PATH)
+            and os.path.getmtime(_LIB_PATH) >= os.path.getmtime(src)):
+        return _LIB_PATH
+    subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = ctypes.CDLL(_LIB_PATH)
+        c_fp = ctypes.POINTER(ctypes.c_float)
+        c_ip = ctypes.POINTER(ctypes.c_int32)
+        c_lp = ctypes.POINTER(ctypes.c_int64)
+        c_dp = ctypes.POINTER(ctypes.c_double)
+        L.gnd_oracle_shift_cloud.argtypes = [c_fp, ctypes.c_int64, ctypes.c_int, ctypes.c_float]
+        L.gnd_oracle_shift_cloud.restype = None
+        L.gnd_oracle_grid_size.argtypes = [c_fp, c_fp, c_ip]
+        L.gnd_oracle_grid_size.restype = None
+        L.gnd_oracle_points_to_voxel.argtypes = [
+            c_fp, ctypes.c_int64, ctypes.c_int, c_fp, c_fp,
+            ctypes.c_int32, ctypes.c_int32, ctypes.c_int,
+            c_fp, c_ip, c_ip, c_ip, c_lp]
+        L.gnd_oracle_points_to_voxel.restype = ctypes.c_int32
+        L.gnd_oracle_segment_cloud.argtypes = [
+            c_fp, ctypes.c_int64, ctypes.c_int, c_dp, ctypes.c_double,
+            c_fp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64,
+            ctypes.c_double, c_dp, c_fp, ctypes.c_int]
+        L.gnd_oracle_segment_cloud.restype = ctypes.c_int64
+        _lib = L
+    return _lib
+
+
+def _fp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _ip(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+
+
+def shift_cloud(cloud, height):
+    """In place, like the reference; returns the same array."""
+    assert cloud.dtype == np.float32 and cloud.flags.c_contiguous and cloud.ndim == 2
+    lib().gnd_oracle_shift_cloud(_fp(cloud), cloud.shape[0], cloud.shape[1], np.float32(height))
+    return cloud
+
+
+def grid_size(voxel_size, coors_range):
+    vs = np.ascontiguousarray(voxel_size, dtype=np.float32)
+    cr = np.ascontiguousarray(coors_range, dtype=np.float32)
+    g = np.zeros(3, dtype=np.int32)
+    lib().gnd_oracle_grid_size(_fp(vs), _fp(cr), _ip(g))
+    return g
+
+
+def points_to_voxel(points, voxel_size, coors_range, max_points=35, reverse_index=True,
+                    max_voxels=20000, return_point_slot=False):
+    """Same signature / outputs as the reference.  float32 points only."""
+    points = np.ascontiguousarray(points)
+    if points.dtype != np.float32:
+        raise TypeError("oracle points_to_voxel restates the float32 path only")
+    vs = np.ascontiguousarray(voxel_size, dtype=np.float32)
+    cr = np.ascontiguousarray(coors_range, dtype=np.float32)
+    g = grid_size(vs, cr)
+    n, cols = points.shape
+    voxels = np.zeros((max_voxels, max_points, cols), dtype=np.float32)
+    coors = np.zeros((max_voxels, 3), dtype=np.int32)
+    npv = np.zeros((max_voxels,), dtype=np.int32)
+    c2v = -np.ones(int(g[0]) * int(g[1]) * int(g[2]), dtype=np.int32)
+    slot = np.empty((n,), dtype=np.int64) if return_point_slot else None
+    m = lib().gnd_oracle_points_to_voxel(
+        _fp(points), n, cols, _fp(vs), _fp(cr), int(max_points), int(max_voxels),
+        1 if reverse_index else 0, _fp(voxels), _ip(coors), _ip(npv), _ip(c2v),
+        slot.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)) if slot is not None else None)
+    out = (voxels[:m], coors[:m], npv[:m])
+    if return_point_slot:
+        return out + (slot,)
+    return out
+
+
+def _segment(points, points_obstacle, grid_size_, voxel_size, elevation_map, threshold):
+    assert points.dtype == np.float32 and points.flags.c_contiguous and points.ndim == 2
+    emap = elevation_map
+    assert emap.dtype == np.float32 and emap.ndim == 2
+    gl = np.array([float(grid_size_[0]), float(grid_size_[1])], dtype=np.float64)
+    labels = np.zeros(points.shape[0], dtype=np.float64)
+    isz = emap.itemsize
+    if points_obstacle is not None:
+        assert points_obstacle.dtype == np.float32 and points_obstacle.flags.c_contiguous
+        po, oc = _fp(points_obstacle), points_obstacle.shape[1]
+    else:
+        po, oc = None, 0
+    # keep the (possibly transposed) view alive; pass its base pointer + strides
+    cnt = lib().gnd_oracle_segment_cloud(
+        _fp(points), points.shape[0], points.shape[1],
+        gl.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), float(voxel_size),
+        ctypes.cast(emap.ctypes.data, ctypes.POINTER(ctypes.c_float)),
+        emap.shape[0], emap.shape[1], emap.strides[0] // isz, emap.strides[1] // isz,
+        float(threshold), labels.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), po, oc)
+    return labels, cnt
+
+
+def segment_cloud(points, grid_size, voxel_size, elevation_map, threshold=0.2):
+    return _segment(points, None, grid_size, voxel_size, elevation_map, threshold)[0]
+
+
+def segment_cloud_noground(points, points_obstacle, grid_size, voxel_size, elevation_map,
+                           threshold=0.2):
+    labels, cnt = _segment(points, points_obstacle, grid_size, voxel_size, elevation_map, threshold)
+    return labels, points_obstacle[:cnt]

@@ -1,0 +1,179 @@
+/*
+ * gnd_oracle.c -- TEST INFRASTRUCTURE ONLY (CPU oracle).
+ *
+ * Plain-C restatement of the integer / index stages of the GndNet inference
+ * hot path.  It exists so that tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs have a checker that travels to the GPU
+ * box (where /root/reference does not exist).  Nothing under gndnet_b200/ may
+ * import, link or call this file.
+ *
+ * Each function cites the reference lines it restates (paths relative to the
+ * reference repo root).  Parity of this restatement is pinned by
+ * oracle/ref_harness.py, which runs the unmodified reference (numba) next to
+ * it in the build container and writes the golden fixtures in tests/golden/.
+ *
+ * Build: see oracle/Makefile  (gcc -O2 -ffp-contract=off, no -ffast-math:
+ * the voxel index arithmetic must be IEEE float32 subtract + divide).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#if defined(__GNUC__)
+#define GND_EXPORT __attribute__((visibility("default")))
+#else
+#define GND_EXPORT
+#endif
+
+/* predict_ground.py:104-107  _shift_cloud: cloud += float32([0,0,h,0]).
+ * Every column gets a float32 add (x+0, y+0, z+h, r+0), so -0.0 becomes +0.0
+ * exactly as in the reference.  cols may be 3 (camera) or 4. */
+GND_EXPORT void gnd_oracle_shift_cloud(float *cloud, int64_t n, int cols, float height)
+{
+    for (int64_t i = 0; i < n; ++i) {
+        volatile float *p = cloud + i * cols;
+        for (int j = 0; j < cols; ++j) {
+            float add = (j == 2) ? height : 0.0f;
+            p[j] = p[j] + add;
+        }
+    }
+}
+
+/* utils/point_cloud_ops.py:24-27 (kernel) and :142-143 (wrapper):
+ * grid = round((hi - lo) / vs) evaluated in the points' dtype (float32),
+ * numpy round == round-half-even == rintf in the default rounding mode. */
+GND_EXPORT void gnd_oracle_grid_size(const float voxel_size[3], const float coors_range[6],
+                                     int32_t grid_xyz[3])
+{
+    for (int j = 0; j < 3; ++j) {
+        volatile float d = coors_range[3 + j] - coors_range[j];
+        volatile float q = d / voxel_size[j];
+        grid_xyz[j] = (int32_t)rintf(q);
+    }
+}
+
+/* utils/point_cloud_ops.py:7-53 (_points_to_voxel_reverse_kernel) and :55-104
+ * (_points_to_voxel_kernel, reverse_index = 0), plus the wrapper's buffer
+ * contract (:147-151): voxels/coors/num_points_per_voxel arrive zero-filled,
+ * coor_to_voxelidx arrives filled with -1 and is shaped (nz,ny,nx) when
+ * reverse_index else (nx,ny,nz).
+ *
+ * point_slot (optional, may be NULL): for every input point, the flat slot
+ * voxelidx*max_points + num it was stored at, or -1 if it was dropped.  Not a
+ * reference output; used by the tests to check the fused CUDA path, which
+ * never materialises the dense voxels tensor.
+ *
+ * Returns voxel_num.  NaN coordinates are undefined behaviour in the
+ * reference (they pass both range tests and index garbage); here, as in the
+ * CUDA path, a point with a NaN coordinate is dropped. */
+GND_EXPORT int32_t gnd_oracle_points_to_voxel(
+    const float *points, int64_t n, int cols,
+    const float voxel_size[3], const float coors_range[6],
+    int32_t max_points, int32_t max_voxels, int reverse_index,
+    float *voxels, int32_t *coors, int32_t *num_points_per_voxel,
+    int32_t *coor_to_voxelidx, int64_t *point_slot)
+{
+    int32_t grid[3];
+    gnd_oracle_grid_size(voxel_size, coors_range, grid);
+    /* extents of coor_to_voxelidx in storage order */
+    int64_t d1, d2;
+    if (reverse_index) { d1 = grid[1]; d2 = grid[0]; }   /* [z][y][x] */
+    else               { d1 = grid[1]; d2 = grid[2]; }   /* [x][y][z] */
+    int32_t voxel_num = 0;
+    int64_t i = 0;
+    for (; i < n; ++i) {
+        const float *p = points + i * cols;
+        int32_t c3[3];
+        int failed = 0;
+        for (int j = 0; j < 3; ++j) {
+            /* :34  c = floor((points[i,j] - coors_range[j]) / voxel_size[j]) in float32 */
+            volatile float d = p[j] - coors_range[j];
+            volatile float q = d / voxel_size[j];
+            float c = floorf(q);
+            /* :35  if c < 0 or c >= grid_size[j] */
+            if (!(c >= 0.0f) || (double)c >= (double)grid[j]) { failed = 1; break; }
+            c3[j] = (int32_t)c;
+        }
+        if (point_slot) point_slot[i] = -1;
+        if (failed) continue;
+        int32_t coor[3];
+        if (reverse_index) { coor[0] = c3[2]; coor[1] = c3[1]; coor[2] = c3[0]; }
+        else               { coor[0] = c3[0]; coor[1] = c3[1]; coor[2] = c3[2]; }
+        int64_t cell = ((int64_t)coor[0] * d1 + coor[1]) * d2 + coor[2];
+        int32_t voxelidx = coor_to_voxelidx[cell];
+        if (voxelidx == -1) {
+            voxelidx = voxel_num;
+            if (voxel_num >= max_voxels) break;            /* :44-45 */
+            voxel_num += 1;
+            coor_to_voxelidx[cell] = voxelidx;
+            coors[voxelidx * 3 + 0] = coor[0];
+            coors[voxelidx * 3 + 1] = coor[1];
+            coors[voxelidx * 3 + 2] = coor[2];
+        }
+        int32_t num = num_points_per_voxel[voxelidx];
+        if (num < max_points) {                            /* :49-52 */
+            if (voxels)
+                memcpy(voxels + ((int64_t)voxelidx * max_points + num) * cols, p,
+                       sizeof(float) * (size_t)cols);
+            if (point_slot) point_slot[i] = (int64_t)voxelidx * max_points + num;
+            num_points_per_voxel[voxelidx] = num + 1;
+        }
+    }
+    if (point_slot) for (int64_t k = i; k < n; ++k) point_slot[k] = -1;
+    return voxel_num;
+}
+
+/* utils/utils.py:198-220  segment_cloud and :222-248 segment_cloud_noground.
+ *
+ * points        [n, cols] float32, C order; columns 0,1 are MUTATED like the
+ *               reference does (:204  lidar_data -= grid_size[:2], rounded to
+ *               float32 because it is an in-place update of a float32 view).
+ * grid_lo       grid_size[0], grid_size[1] as the doubles numpy/numba see.
+ * voxel_size    Python scalar -> double (:205 divides in float64).
+ * emap          elevation_map as the reference indexes it: emap[x, y], given
+ *               with explicit element strides (the callers pass pred.T, an
+ *               F-ordered view, predict_ground.py:168).
+ * labels        float64 [n]  (np.zeros default dtype, :201).
+ * points_obstacle  NULL for segment_cloud; else [n, ocols] compacted in place
+ *               (:242-243), return value = obs_cnt.
+ */
+GND_EXPORT int64_t gnd_oracle_segment_cloud(
+    float *points, int64_t n, int cols,
+    const double grid_lo[2], double voxel_size,
+    const float *emap, int64_t emap_nx, int64_t emap_ny, int64_t emap_sx, int64_t emap_sy,
+    double threshold, double *labels,
+    float *points_obstacle, int ocols)
+{
+    int64_t obs_cnt = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        float *p = points + i * cols;
+        int32_t cell[2];
+        for (int j = 0; j < 2; ++j) {
+            float shifted = (float)((double)p[j] - grid_lo[j]);   /* :204 */
+            p[j] = shifted;
+            double q = floor((double)shifted / voxel_size);        /* :205-206 */
+            /* :207 astype(int32): x86 cvttsd2si semantics for out-of-range / NaN */
+            int32_t ci;
+            if (!(q >= -2147483648.0 && q <= 2147483647.0)) ci = INT32_MIN;
+            else ci = (int32_t)q;
+            cell[j] = ci;
+        }
+        int32_t x = cell[0], y = cell[1];
+        if (0 < x && x < emap_nx && 0 < y && y < emap_ny) {        /* :213 */
+            double h = (double)emap[x * emap_sx + y * emap_sy];
+            if ((double)p[2] > h + threshold) {                    /* :214 */
+                labels[i] = 1.0;
+                if (points_obstacle) {
+                    memmove(points_obstacle + obs_cnt * ocols, points_obstacle + i * ocols,
+                            sizeof(float) * (size_t)ocols);
+                    obs_cnt += 1;
+                }
+            } else {
+                labels[i] = 0.0;
+            }
+        } else {
+            labels[i] = -1.0;                                      /* :219 */
+        }
+    }
+    return obs_cnt;
+}
