@@ -1,0 +1,89 @@
+// model.cuh -- the model context (weights, workspace carving, stage buffers) shared by the
+// pillar-encode, segnet and ABI translation units.
+#pragma once
+#include "common.cuh"
+#include "voxelize.cuh"
+#include <cuda.h>
+#include <string>
+#include <vector>
+
+namespace gnd {
+
+constexpr int PFN_OUT = 64;        // cfg.vfe_filters = [64] in every shipped config
+constexpr int PFN_MAX_FEAT = 10;   // F(<=4) + 3 + 2 + with_distance
+
+// A BEV activation tensor, NHWC ([B][H][W][C]).  fp32 mode: one float plane.  tcgen05 modes: an fp16
+// "hi" plane and (for split-fp16 consumers) an fp16 "lo" plane with value = hi + lo.
+struct Act {
+    float *f32 = nullptr;
+    __half *hi = nullptr;
+    __half *lo = nullptr;
+    int H = 0, W = 0, C = 0;
+    size_t elems(int B) const { return (size_t)B * H * W * C; }
+};
+
+struct ConvLayer {
+    const char *name;       // state_dict prefix under encoder_decoder.
+    int cin, cout;
+    float *w32 = nullptr;   // [9][cin][cout] fp32, BatchNorm folded           (fp32 mode)
+    __half *whi = nullptr;  // [9][cout][cin] fp16 hi, K-major for UMMA        (tcgen05 modes)
+    __half *wlo = nullptr;  // [9][cout][cin] fp16 lo
+    float *bias = nullptr;  // [cout] folded bias
+    int split = 0;          // tcgen05: 1 = three-product split-fp16, 0 = single fp16 product
+};
+
+struct TensorMaps;   // conv_tc.cu
+
+}  // namespace gnd
+
+struct gnd_ctx {
+    gnd_config cfg;
+    int device = 0;
+    int nx = 0, ny = 0, nz = 0;
+    int H1 = 0, W1 = 0, H2 = 0, W2 = 0;      // pooled sizes (floor)
+    int nfeat = 0;                           // PFN input features
+    gnd_voxel_params vparams;
+
+    // weights (device)
+    bool weights_loaded = false;
+    float *pfn_w = nullptr;    // [nfeat][64], BatchNorm1d folded when use_norm
+    float *pfn_b = nullptr;    // [64]
+    gnd::ConvLayer conv[8];
+    float *reg_w = nullptr;    // [9][64]
+    float *reg_b = nullptr;    // [1]
+    void *weight_blob = nullptr;
+
+    // bound workspace
+    void *ws = nullptr;
+    size_t ws_bytes = 0;
+    int B = 0;
+    int64_t N = 0;
+    gnd::VoxPlan vplan;
+    gnd::VoxWs vws;
+    int32_t *coors = nullptr, *num_points = nullptr, *voxel_count = nullptr, *offsets = nullptr, *list = nullptr;
+    gnd::Act canvas, d1a, d1b, p1, d2a, d2b, u2, u2a, u2b, u1, u1a, u1b;
+    uint8_t *idx1 = nullptr;   // [B][H1][W1][128] argmax (0..3) of down1's pool
+    float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
+    gnd::TensorMaps *tmaps = nullptr;
+
+    int last_launches = 0;
+};
+
+namespace gnd {
+
+// pfn.cu
+int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_points, cudaStream_t st);
+int pfn_scatter_dense_run(gnd_ctx *ctx, const float *voxels, const float *coors4, const float *num_points,
+                          int64_t n_pillars, int32_t batch, cudaStream_t st);
+// segnet.cu
+int segnet_run(gnd_ctx *ctx, int32_t batch, float *height, cudaStream_t st);
+// conv_tc.cu (tcgen05 path)
+int tc_build_tensor_maps(gnd_ctx *ctx);
+void tc_free_tensor_maps(gnd_ctx *ctx);
+int tc_conv_run(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
+// segment.cu
+int segment_run(const gnd_segment_params *p, float *points, const int32_t *counts, int32_t batch,
+                int64_t n_points, const float *elevation, double *labels_f64, int8_t *labels_i8,
+                cudaStream_t stream);
+
+}  // namespace gnd

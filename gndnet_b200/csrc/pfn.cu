@@ -1,0 +1,255 @@
+// pfn.cu -- PillarFeatureNet + PointPillarsScatter as one kernel.
+//
+// Replaces modules/pointpillars.py:115-146 (PillarFeatureNet.forward), :52-65 (PFNLayer.forward),
+// :202-223 (get_paddings_indicator) and :168-199 (PointPillarsScatter.forward).
+//
+//   features = [x, y, z, (r), x-mean_x, y-mean_y, z-mean_z, x-cx, y-cy, (|xyz|)]        (:120-133)
+//   mean     = sum over the pillar's slots / num_points                                   (:120)
+//   cx, cy   = coors_x * vx + (vx/2 + pc_range[0]),  coors_y * vy + (vy/2 + pc_range[1])  (:110-113, :125-126)
+//   padded slots are zeroed BEFORE the Linear, so they contribute relu(bias') to the max whenever
+//   num_points < max_points                                                              (:137-140, :54-58)
+//   out[ch]  = max over slots of relu(W' f + b')   (BatchNorm1d folded into W', b' when use_norm)
+//   canvas[b, :, y, x] = out                                                             (:174-189)
+//
+// One warp per BEV cell: lane l owns channels 2l, 2l+1 (18-20 weights in registers); the pillar's
+// points are gathered through the voxelizer's pillar list, decorated by one lane each, staged in
+// shared memory and broadcast to all lanes; the 64-channel result is written as one coalesced
+// 128/256-byte NHWC row -- and empty cells get their zeros from the same kernel, so the canvas needs
+// no separate memset.  HBM-bound: <= 16 B read per kept point + 64*e B written per cell.
+#include "model.cuh"
+
+namespace gnd {
+
+struct PfnArgs {
+    const float *points;        // fused: [B][N][F] raw scans    dense: voxels [M][P][F]
+    int32_t B;
+    int64_t N;
+    int32_t F;
+    int32_t nfeat;
+    int32_t with_distance;
+    int32_t P;                  // max_points_voxel
+    int32_t max_voxels;
+    int32_t nx, ny;
+    float vx, vy, xoff, yoff;
+    int32_t apply_shift;
+    float z_shift;
+    const float *w;             // [nfeat][64]
+    const float *bias;          // [64]
+    // fused inputs
+    const int32_t *vid, *num, *off, *list;
+    // dense inputs
+    const float *coors4, *num_f;
+    int64_t M;
+    // output canvas [B][ny][nx][64]
+    float *out32;
+    __half *out_hi, *out_lo;
+};
+
+constexpr int PFN_WARPS = 8;
+constexpr int FEAT_STRIDE = 12;
+
+__device__ __forceinline__ void store_cell(const PfnArgs &a, int64_t cell_global, int lane, float m0, float m1) {
+    const int64_t o = cell_global * PFN_OUT + 2 * lane;
+    if (a.out32) {
+        *reinterpret_cast<float2 *>(a.out32 + o) = make_float2(m0, m1);
+    } else {
+        __half h0 = __float2half_rn(m0), h1 = __float2half_rn(m1);
+        *reinterpret_cast<__half2 *>(a.out_hi + o) = __halves2half2(h0, h1);
+        if (a.out_lo) {
+            __half l0 = __float2half_rn(m0 - __half2float(h0)), l1 = __float2half_rn(m1 - __half2float(h1));
+            *reinterpret_cast<__half2 *>(a.out_lo + o) = __halves2half2(l0, l1);
+        }
+    }
+}
+
+__device__ __forceinline__ void load_point(const float *row, int F, bool vec4, float &x, float &y, float &z, float &r) {
+    if (vec4) {
+        float4 v = __ldg(reinterpret_cast<const float4 *>(row));
+        x = v.x; y = v.y; z = v.z; r = v.w;
+    } else {
+        x = __ldg(row); y = __ldg(row + 1); z = __ldg(row + 2);
+        r = (F > 3) ? __ldg(row + 3) : 0.0f;
+    }
+}
+
+// Shared by both kernels: given a way to fetch slot j's point, run the pillar through the PFN layer.
+// fetch(j, x, y, z, r) must be callable by any lane for j < n_real.
+template <typename Fetch>
+__device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s_feat)[FEAT_STRIDE], const float *wreg0,
+                                           const float *wreg1, float b0, float b1, int n_real, float sumx, float sumy,
+                                           float sumz, float n_div, float cxf, float cyf, Fetch fetch, float &m0, float &m1) {
+    // :120 points_mean = sum / num_voxels (float32 division)
+    const float mx = __fdiv_rn(sumx, n_div), my = __fdiv_rn(sumy, n_div), mz = __fdiv_rn(sumz, n_div);
+    // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
+    const float pcx = __fadd_rn(__fmul_rn(cxf, a.vx), a.xoff);
+    const float pcy = __fadd_rn(__fmul_rn(cyf, a.vy), a.yoff);
+    // padded slots give relu(b') (:137-140 then :54-58); with none padded the relu floor is 0
+    m0 = (n_real < a.P) ? fmaxf(b0, 0.0f) : 0.0f;
+    m1 = (n_real < a.P) ? fmaxf(b1, 0.0f) : 0.0f;
+    for (int j0 = 0; j0 < n_real; j0 += 32) {
+        const int j = j0 + lane;
+        if (j < n_real) {
+            float x, y, z, r;
+            fetch(j, x, y, z, r);
+            float *f = s_feat[lane];
+            int k = 0;
+            f[k++] = x; f[k++] = y; f[k++] = z;
+            if (a.F > 3) f[k++] = r;
+            f[k++] = __fsub_rn(x, mx); f[k++] = __fsub_rn(y, my); f[k++] = __fsub_rn(z, mz);
+            f[k++] = __fsub_rn(x, pcx); f[k++] = __fsub_rn(y, pcy);
+            if (a.with_distance) f[k++] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+        }
+        __syncwarp();
+        const int cnt = min(32, n_real - j0);
+        for (int p = 0; p < cnt; ++p) {
+            const float *f = s_feat[p];
+            float y0 = b0, y1 = b1;
+#pragma unroll
+            for (int k = 0; k < PFN_MAX_FEAT; ++k)
+                if (k < a.nfeat) { y0 = fmaf(wreg0[k], f[k], y0); y1 = fmaf(wreg1[k], f[k], y1); }
+            m0 = fmaxf(m0, y0);
+            m1 = fmaxf(m1, y1);
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnArgs a) {
+    __shared__ float s_feat[PFN_WARPS][32][FEAT_STRIDE];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float w0[PFN_MAX_FEAT], w1[PFN_MAX_FEAT];
+#pragma unroll
+    for (int k = 0; k < PFN_MAX_FEAT; ++k) {
+        w0[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane) : 0.0f;
+        w1[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane + 1) : 0.0f;
+    }
+    const float b0 = __ldg(a.bias + 2 * lane), b1 = __ldg(a.bias + 2 * lane + 1);
+    const int cells = a.nx * a.ny;
+    const int64_t total = (int64_t)a.B * cells;
+    const bool vec4 = (a.F == 4) && ((((uintptr_t)a.points) & 15) == 0);
+    for (int64_t g = (int64_t)blockIdx.x * PFN_WARPS + warp; g < total; g += (int64_t)gridDim.x * PFN_WARPS) {
+        const int b = (int)(g / cells), c = (int)(g - (int64_t)b * cells);
+        const int v = __ldg(a.vid + g);
+        float m0 = 0.0f, m1 = 0.0f;
+        if (v >= 0) {
+            const int n = __ldg(a.num + (int64_t)b * a.max_voxels + v);
+            const int o = __ldg(a.off + (int64_t)b * (a.max_voxels + 1) + v);
+            const int32_t *lst = a.list + (int64_t)b * a.N + o;
+            const float *pts = a.points + (int64_t)b * a.N * a.F;
+            auto fetch = [&](int j, float &x, float &y, float &z, float &r) {
+                const int i = __ldg(lst + j);
+                load_point(pts + (int64_t)i * a.F, a.F, vec4, x, y, z, r);
+                if (a.apply_shift) z = __fadd_rn(z, a.z_shift);
+            };
+            float sx = 0.f, sy = 0.f, sz = 0.f;
+            for (int j = lane; j < n; j += 32) {
+                float x, y, z, r;
+                fetch(j, x, y, z, r);
+                sx += x; sy += y; sz += z;
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                sx += __shfl_xor_sync(0xffffffffu, sx, d);
+                sy += __shfl_xor_sync(0xffffffffu, sy, d);
+                sz += __shfl_xor_sync(0xffffffffu, sz, d);
+            }
+            pfn_pillar(a, lane, s_feat[warp], w0, w1, b0, b1, n, sx, sy, sz, (float)n, (float)(c % a.nx),
+                       (float)(c / a.nx), fetch, m0, m1);
+        }
+        store_cell(a, g, lane, m0, m1);
+    }
+}
+
+// Drop-in tensors (model.py:36-42): voxels [M][P][F], coors [M][4] float (b,z,y,x), num_points [M] float.
+// The canvas must have been zero-filled (pointpillars.py:174).
+__global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_dense_kernel(const PfnArgs a) {
+    __shared__ float s_feat[PFN_WARPS][32][FEAT_STRIDE];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float w0[PFN_MAX_FEAT], w1[PFN_MAX_FEAT];
+#pragma unroll
+    for (int k = 0; k < PFN_MAX_FEAT; ++k) {
+        w0[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane) : 0.0f;
+        w1[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane + 1) : 0.0f;
+    }
+    const float b0 = __ldg(a.bias + 2 * lane), b1 = __ldg(a.bias + 2 * lane + 1);
+    const bool vec4 = (a.F == 4) && ((((uintptr_t)a.points) & 15) == 0);
+    for (int64_t m = (int64_t)blockIdx.x * PFN_WARPS + warp; m < a.M; m += (int64_t)gridDim.x * PFN_WARPS) {
+        const float *vox = a.points + m * a.P * a.F;
+        const float nf = __ldg(a.num_f + m);
+        const int n = max(0, min(a.P, (int)nf));                    // num_voxels.int() > arange (:202-223)
+        const float bf = __ldg(a.coors4 + m * 4 + 0), cyf = __ldg(a.coors4 + m * 4 + 2), cxf = __ldg(a.coors4 + m * 4 + 3);
+        const int b = (int)bf;
+        const int64_t cell = (int64_t)(__fadd_rn(__fmul_rn(cyf, (float)a.nx), cxf));   // y*nx + x (:180)
+        auto fetch = [&](int j, float &x, float &y, float &z, float &r) {
+            load_point(vox + (int64_t)j * a.F, a.F, vec4, x, y, z, r);
+        };
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+        for (int j = lane; j < a.P; j += 32) {      // :120 sums every slot, padded ones included
+            float x, y, z, r;
+            fetch(j, x, y, z, r);
+            sx += x; sy += y; sz += z;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            sx += __shfl_xor_sync(0xffffffffu, sx, d);
+            sy += __shfl_xor_sync(0xffffffffu, sy, d);
+            sz += __shfl_xor_sync(0xffffffffu, sz, d);
+        }
+        float m0, m1;
+        pfn_pillar(a, lane, s_feat[warp], w0, w1, b0, b1, n, sx, sy, sz, nf, cxf, cyf, fetch, m0, m1);
+        if (b >= 0 && b < a.B && cell >= 0 && cell < (int64_t)a.nx * a.ny)
+            store_cell(a, (int64_t)b * a.nx * a.ny + cell, lane, m0, m1);
+    }
+}
+
+static void fill_common(const gnd_ctx *ctx, PfnArgs &a, int32_t batch) {
+    const gnd_config &c = ctx->cfg;
+    a.B = batch;
+    a.F = c.input_features;
+    a.nfeat = ctx->nfeat;
+    a.with_distance = c.with_distance;
+    a.P = c.max_points_voxel;
+    a.max_voxels = c.max_voxels;
+    a.nx = ctx->nx; a.ny = ctx->ny;
+    // pointpillars.py:110-113: Python-float arithmetic, then float32 when it meets the tensors
+    a.vx = (float)c.voxel_size_f64[0];
+    a.vy = (float)c.voxel_size_f64[1];
+    a.xoff = (float)(c.voxel_size_f64[0] / 2 + c.pc_range_f64[0]);
+    a.yoff = (float)(c.voxel_size_f64[1] / 2 + c.pc_range_f64[1]);
+    a.w = ctx->pfn_w; a.bias = ctx->pfn_b;
+    a.out32 = ctx->canvas.f32; a.out_hi = ctx->canvas.hi; a.out_lo = ctx->canvas.lo;
+}
+
+int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_points, cudaStream_t st) {
+    if (ctx->nz != 1) return fail(GND_ERR_UNSUPPORTED, "pillar scatter needs a single z layer (nz=%d)", ctx->nz);
+    PfnArgs a = {};
+    fill_common(ctx, a, batch);
+    a.points = points; a.N = n_points;
+    a.apply_shift = 1; a.z_shift = ctx->cfg.lidar_height;
+    a.vid = ctx->vws.vid; a.num = ctx->num_points; a.off = ctx->offsets; a.list = ctx->list;
+    int64_t warps = (int64_t)batch * ctx->nx * ctx->ny;
+    int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    pfn_scatter_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+    GND_LAUNCH_CHECK("pfn_scatter_kernel");
+    return GND_OK;
+}
+
+int pfn_scatter_dense_run(gnd_ctx *ctx, const float *voxels, const float *coors4, const float *num_points,
+                          int64_t n_pillars, int32_t batch, cudaStream_t st) {
+    PfnArgs a = {};
+    fill_common(ctx, a, batch);
+    a.points = voxels; a.coors4 = coors4; a.num_f = num_points; a.M = n_pillars;
+    const size_t n = ctx->canvas.elems(batch);
+    if (a.out32) GND_CUDA_CHECK(cudaMemsetAsync(a.out32, 0, n * sizeof(float), st));
+    if (a.out_hi) GND_CUDA_CHECK(cudaMemsetAsync(a.out_hi, 0, n * sizeof(__half), st));
+    if (a.out_lo) GND_CUDA_CHECK(cudaMemsetAsync(a.out_lo, 0, n * sizeof(__half), st));
+    if (n_pillars == 0) return GND_OK;
+    int blocks = (int)((n_pillars + PFN_WARPS - 1) / PFN_WARPS);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    pfn_scatter_dense_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+    GND_LAUNCH_CHECK("pfn_scatter_dense_kernel");
+    return GND_OK;
+}
+
+}  // namespace gnd

@@ -1,0 +1,166 @@
+// segment.cu -- per-point ground / obstacle labelling against the estimated height map.
+//
+// Replaces utils/utils.py:198-220 (segment_cloud) and :222-248 (segment_cloud_noground).
+// Arithmetic restated exactly:
+//   :204  xy -= grid_size[:2]     float32 array minus int64 array: float64 subtract rounded back to float32
+//   :205  / voxel_size            float64 division by the Python scalar
+//   :206-207 floor, astype(int32)
+//   :213  0 < x < nx and 0 < y < ny      (index 0 is OUT of range)
+//   :214  z > elevation_map[x, y] + threshold    in float64
+// HBM-bound gather: 12-16 B read + 1-8 B written per point, the 40 KB map stays in L1/L2.
+#include "common.cuh"
+#include <limits.h>
+
+namespace gnd {
+
+struct SegArgs {
+    gnd_segment_params p;
+    float *points;
+    const int32_t *counts;
+    int32_t B;
+    int64_t N;
+    const float *elev;
+    double *lab64;
+    int8_t *lab8;
+};
+
+__device__ __forceinline__ int seg_axis(float v, double lo, double vs, float *shifted) {
+    float s = __double2float_rn((double)v - lo);          // :204 (in-place float32 update)
+    *shifted = s;
+    double q = floor((double)s / vs);                     // :205-206
+    if (!(q >= -2147483648.0 && q <= 2147483647.0)) return INT_MIN;   // :207 cvttsd2si semantics
+    return (int)q;
+}
+
+__global__ void __launch_bounds__(256) segment_kernel(const SegArgs a) {
+    const int64_t total = (int64_t)a.B * a.N;
+    const int F = a.p.num_features;
+    for (int64_t gi = (int64_t)blockIdx.x * 256 + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * 256) {
+        const int b = (int)(gi / a.N);
+        const int64_t i = gi - (int64_t)b * a.N;
+        int label = -1;
+        const int n = a.counts ? a.counts[b] : (int)a.N;
+        if (i < n) {
+            float *row = a.points + gi * F;
+            float x, y, z;
+            if (F == 4 && (((uintptr_t)a.points) & 15) == 0) {
+                float4 v = *reinterpret_cast<const float4 *>(row);
+                x = v.x; y = v.y; z = v.z;
+            } else {
+                x = row[0]; y = row[1]; z = row[2];
+            }
+            if (a.p.apply_z_shift) z = __fadd_rn(z, a.p.z_shift);
+            float sx, sy;
+            const int cx = seg_axis(x, a.p.grid_lo[0], a.p.voxel_size, &sx);
+            const int cy = seg_axis(y, a.p.grid_lo[1], a.p.voxel_size, &sy);
+            if (a.p.mutate_points) { row[0] = sx; row[1] = sy; }
+            if (0 < cx && cx < a.p.map_nx && 0 < cy && cy < a.p.map_ny) {   // :213
+                const float h = __ldg(a.elev + (int64_t)b * a.p.map_batch_stride + cx * a.p.map_sx + cy * a.p.map_sy);
+                label = ((double)z > (double)h + a.p.threshold) ? 1 : 0;     // :214-217
+            }
+        }
+        if (a.lab8) a.lab8[gi] = (int8_t)label;
+        if (a.lab64) a.lab64[gi] = (double)label;
+    }
+}
+
+// ---- stable obstacle compaction (:242-243, :248) ----------------------------------------------
+constexpr int CMP_BLOCK = 1024;
+
+__global__ void __launch_bounds__(CMP_BLOCK) compact_count_kernel(const int8_t *lab, int64_t n, int32_t *block_counts) {
+    __shared__ int s_warp[33];
+    int64_t i = (int64_t)blockIdx.x * CMP_BLOCK + threadIdx.x;
+    int flag = (i < n && lab[i] == 1) ? 1 : 0;
+    int total;
+    block_exclusive_scan(flag, s_warp, &total);
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) compact_scan_kernel(int32_t *block_counts, int nblocks, int32_t *obstacle_count) {
+    __shared__ int s_warp[33];
+    int carry = 0;
+    for (int base = 0; base < nblocks; base += 1024) {
+        int idx = base + threadIdx.x;
+        int v = idx < nblocks ? block_counts[idx] : 0;
+        int total;
+        int ex = block_exclusive_scan(v, s_warp, &total);
+        if (idx < nblocks) block_counts[idx] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) *obstacle_count = carry;
+}
+
+__global__ void __launch_bounds__(CMP_BLOCK) compact_write_kernel(const int8_t *lab, const float *src, int64_t n, int F,
+                                                                 const int32_t *block_offsets, float *dst) {
+    __shared__ int s_warp[33];
+    int64_t i = (int64_t)blockIdx.x * CMP_BLOCK + threadIdx.x;
+    int flag = (i < n && lab[i] == 1) ? 1 : 0;
+    int total;
+    int ex = block_exclusive_scan(flag, s_warp, &total);
+    if (flag) {
+        int64_t o = (int64_t)block_offsets[blockIdx.x] + ex;
+        for (int f = 0; f < F; ++f) dst[o * F + f] = src[i * F + f];
+    }
+}
+
+int segment_run(const gnd_segment_params *p, float *points, const int32_t *counts, int32_t batch,
+                int64_t n_points, const float *elevation, double *labels_f64, int8_t *labels_i8,
+                cudaStream_t stream) {
+    if (!p) return fail(GND_ERR_INVALID, "null segment params");
+    if (batch < 1 || n_points < 0) return fail(GND_ERR_INVALID, "bad batch / n_points");
+    if (p->num_features < 3) return fail(GND_ERR_INVALID, "points need >= 3 columns");
+    if (!(p->voxel_size > 0.0)) return fail(GND_ERR_INVALID, "voxel_size must be > 0");
+    if (p->map_nx < 1 || p->map_ny < 1) return fail(GND_ERR_INVALID, "empty elevation map");
+    if (n_points == 0) return GND_OK;
+    if (!points || !elevation) return fail(GND_ERR_INVALID, "null points / elevation");
+    if (!labels_f64 && !labels_i8) return fail(GND_ERR_INVALID, "no label output given");
+    SegArgs a;
+    a.p = *p; a.points = points; a.counts = counts; a.B = batch; a.N = n_points;
+    a.elev = elevation; a.lab64 = labels_f64; a.lab8 = labels_i8;
+    int64_t total = (int64_t)batch * n_points;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    segment_kernel<<<blocks, 256, 0, stream>>>(a);
+    GND_LAUNCH_CHECK("segment_kernel");
+    return GND_OK;
+}
+
+}  // namespace gnd
+
+using namespace gnd;
+
+extern "C" int gnd_segment_cloud(const gnd_segment_params *p, float *points, const int32_t *counts,
+                                 int32_t batch, int64_t n_points, const float *elevation,
+                                 double *labels_f64, int8_t *labels_i8, void *stream) {
+    g_launches = 0;
+    return segment_run(p, points, counts, batch, n_points, elevation, labels_f64, labels_i8, (cudaStream_t)stream);
+}
+
+extern "C" int gnd_compact_workspace_bytes(int64_t n_points, size_t *h_bytes) {
+    if (!h_bytes || n_points < 0) return fail(GND_ERR_INVALID, "bad argument");
+    *h_bytes = align_up((size_t)((n_points + CMP_BLOCK - 1) / CMP_BLOCK + 1) * sizeof(int32_t), 256);
+    return GND_OK;
+}
+
+extern "C" int gnd_compact_obstacles(const int8_t *labels_i8, const float *points_obstacle, int64_t n_points,
+                                     int32_t obstacle_features, void *workspace, size_t workspace_bytes,
+                                     float *out_obstacle, int32_t *obstacle_count, void *stream) {
+    g_launches = 0;
+    if (n_points < 0 || obstacle_features < 1) return fail(GND_ERR_INVALID, "bad shape");
+    if (!obstacle_count) return fail(GND_ERR_INVALID, "obstacle_count is null");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_points == 0) { GND_CUDA_CHECK(cudaMemsetAsync(obstacle_count, 0, sizeof(int32_t), st)); return GND_OK; }
+    if (!labels_i8 || !points_obstacle || !out_obstacle) return fail(GND_ERR_INVALID, "null pointer");
+    size_t need;
+    gnd_compact_workspace_bytes(n_points, &need);
+    if (!workspace || workspace_bytes < need) return fail(GND_ERR_WORKSPACE, "compaction workspace: need %zu bytes", need);
+    int nblocks = (int)((n_points + CMP_BLOCK - 1) / CMP_BLOCK);
+    int32_t *bc = (int32_t *)workspace;
+    compact_count_kernel<<<nblocks, CMP_BLOCK, 0, st>>>(labels_i8, n_points, bc);
+    GND_LAUNCH_CHECK("compact_count_kernel");
+    compact_scan_kernel<<<1, 1024, 0, st>>>(bc, nblocks, obstacle_count);
+    GND_LAUNCH_CHECK("compact_scan_kernel");
+    compact_write_kernel<<<nblocks, CMP_BLOCK, 0, st>>>(labels_i8, points_obstacle, n_points, obstacle_features, bc, out_obstacle);
+    GND_LAUNCH_CHECK("compact_write_kernel");
+    return GND_OK;
+}

@@ -1,0 +1,272 @@
+// segnet.cu -- segnetGndEst.forward (modules/segnet.py:133-142): schedule of the encoder/decoder,
+// the pooling / unpooling kernels, the regression head, and the strict-fp32 CUDA-core convolution.
+//
+//   down1 = conv(64->128), conv(128->128), maxpool 2x2 + indices          (segnet.py:49-61)
+//   down2 = conv(128->256), conv(256->256), maxpool 2x2 + indices
+//   up2   = unpool(indices2), conv(256->256), conv(256->128)               (segnet.py:81-92)
+//   up1   = unpool(indices1), conv(128->128), conv(128->64)
+//   regressor conv(64->1), no BatchNorm / ReLU                             (segnet.py:131,140)
+// every conv is 3x3, stride 1, zero pad 1, bias, BatchNorm2d(eval, eps 1e-5) folded at load, ReLU
+// (segnet.py:11-44).  MaxPool2d(2,2) floors odd sizes and keeps the FIRST maximum in row-major window
+// order; MaxUnpool2d writes the value back at that position of a zero tensor of the pre-pool shape.
+// pool(down2) followed at once by unpool is a mask: keep the window's first maximum, zero the rest.
+//
+// All activations are NHWC.  The tcgen05 implicit-GEMM convolutions live in conv_tc.cu; this file
+// holds the fp32 mode (GND_PREC_FP32), which is the 1e-3 m parity path.
+#include "model.cuh"
+
+namespace gnd {
+
+// ---- element access for either activation format ------------------------------------------
+__device__ __forceinline__ float act_load(const Act &a, size_t i) {
+    if (a.f32) return a.f32[i];
+    float v = __half2float(a.hi[i]);
+    if (a.lo) v += __half2float(a.lo[i]);     // exact: hi and lo are adjacent 11-bit pieces
+    return v;
+}
+__device__ __forceinline__ void act_store(const Act &a, size_t i, float v) {
+    if (a.f32) { a.f32[i] = v; return; }
+    __half h = __float2half_rn(v);
+    a.hi[i] = h;
+    if (a.lo) a.lo[i] = __float2half_rn(v - __half2float(h));
+}
+
+// first maximum of the 2x2 window in row-major order, strict '>' (ATen max_pool2d)
+__device__ __forceinline__ int window_argmax(float v00, float v01, float v10, float v11, float *vmax) {
+    int k = 0; float m = v00;
+    if (v01 > m) { m = v01; k = 1; }
+    if (v10 > m) { m = v10; k = 2; }
+    if (v11 > m) { m = v11; k = 3; }
+    *vmax = m;
+    return k;
+}
+
+// MaxPool2d(2,2,return_indices) (segnet.py:54,60): in [B][H][W][C] -> out [B][H/2][W/2][C] + argmax 0..3
+__global__ void __launch_bounds__(256) pool_kernel(const Act in, const Act out, uint8_t *idx, int B) {
+    const int C = in.C, Ho = out.H, Wo = out.W;
+    const size_t total = (size_t)B * Ho * Wo * C;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C);
+        size_t p = g / C;
+        const int wo = (int)(p % Wo); p /= Wo;
+        const int ho = (int)(p % Ho);
+        const int b = (int)(p / Ho);
+        const size_t r0 = (((size_t)b * in.H + 2 * ho) * in.W + 2 * wo) * C + c;
+        const size_t r1 = r0 + (size_t)in.W * C;
+        float m;
+        int k = window_argmax(act_load(in, r0), act_load(in, r0 + C), act_load(in, r1), act_load(in, r1 + C), &m);
+        act_store(out, g, m);
+        idx[g] = (uint8_t)k;
+    }
+}
+
+// pool + unpool back to the same shape (down2 -> up2): out[h][w] = in[h][w] if it is its window's first max else 0
+__global__ void __launch_bounds__(256) pool_mask_kernel(const Act in, const Act out, int B) {
+    const int C = in.C, H = in.H, W = in.W, Hp = H / 2, Wp = W / 2;
+    const size_t total = (size_t)B * H * W * C;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C);
+        size_t p = g / C;
+        const int w = (int)(p % W); p /= W;
+        const int h = (int)(p % H);
+        const int b = (int)(p / H);
+        float v = 0.0f;
+        if ((h >> 1) < Hp && (w >> 1) < Wp) {
+            const size_t r0 = (((size_t)b * H + (h & ~1)) * W + (w & ~1)) * C + c;
+            const size_t r1 = r0 + (size_t)W * C;
+            float m;
+            int k = window_argmax(act_load(in, r0), act_load(in, r0 + C), act_load(in, r1), act_load(in, r1 + C), &m);
+            if (k == ((h & 1) * 2 + (w & 1))) v = m;
+        }
+        act_store(out, g, v);
+    }
+}
+
+// MaxUnpool2d(2,2) to the recorded shape (segnet.py:84,89): in [B][Hp][Wp][C] + idx -> out [B][H][W][C]
+__global__ void __launch_bounds__(256) unpool_kernel(const Act in, const uint8_t *idx, const Act out, int B) {
+    const int C = out.C, H = out.H, W = out.W, Hp = in.H, Wp = in.W;
+    const size_t total = (size_t)B * H * W * C;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C);
+        size_t p = g / C;
+        const int w = (int)(p % W); p /= W;
+        const int h = (int)(p % H);
+        const int b = (int)(p / H);
+        float v = 0.0f;
+        if ((h >> 1) < Hp && (w >> 1) < Wp) {
+            const size_t s = (((size_t)b * Hp + (h >> 1)) * Wp + (w >> 1)) * C + c;
+            if (idx[s] == ((h & 1) * 2 + (w & 1))) v = act_load(in, s);
+        }
+        act_store(out, g, v);
+    }
+}
+
+// ---- strict fp32 convolution: 8x8 pixels x 64 output channels per CTA, 4x4 outputs per thread ----
+__global__ void __launch_bounds__(256) conv3x3_f32_kernel(const float *__restrict__ in, const float *__restrict__ w,
+                                                          const float *__restrict__ bias, float *__restrict__ out,
+                                                          int H, int W, int Cin, int Cout, int relu) {
+    __shared__ __align__(16) float s_in[100][16];
+    __shared__ __align__(16) float s_w[9][16][64];
+    const int tiles_w = (W + 7) / 8;
+    const int h0 = (blockIdx.x / tiles_w) * 8, w0 = (blockIdx.x % tiles_w) * 8;
+    const int n0 = blockIdx.y * 64, b = blockIdx.z;
+    const int tid = threadIdx.x, tc = tid & 15, tp = tid >> 4;
+    const int prow = tp >> 1, pcol0 = (tp & 1) * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc[p][k] = 0.0f;
+
+    for (int c0 = 0; c0 < Cin; c0 += 16) {
+        for (int q = tid; q < 400; q += 256) {
+            const int pix = q >> 2, c4 = (q & 3) * 4;
+            const int gh = h0 + pix / 10 - 1, gw = w0 + pix % 10 - 1;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gh >= 0 && gh < H && gw >= 0 && gw < W)
+                v = __ldg(reinterpret_cast<const float4 *>(in + (((size_t)b * H + gh) * W + gw) * Cin + c0 + c4));
+            *reinterpret_cast<float4 *>(&s_in[pix][c4]) = v;
+        }
+        for (int q = tid; q < 2304; q += 256) {
+            const int row = q >> 4, c4 = (q & 15) * 4;
+            const int tap = row >> 4, ci = row & 15;
+            *reinterpret_cast<float4 *>(&s_w[tap][ci][c4]) =
+                __ldg(reinterpret_cast<const float4 *>(w + ((size_t)tap * Cin + c0 + ci) * Cout + n0 + c4));
+        }
+        __syncthreads();
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap % 3;
+#pragma unroll
+            for (int ci = 0; ci < 16; ci += 4) {
+                float4 a[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    a[p] = *reinterpret_cast<const float4 *>(&s_in[(prow + kh) * 10 + pcol0 + p + kw][ci]);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float4 bw = *reinterpret_cast<const float4 *>(&s_w[tap][ci + k][tc * 4]);
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) {
+                        const float av = (k == 0) ? a[p].x : (k == 1) ? a[p].y : (k == 2) ? a[p].z : a[p].w;
+                        acc[p][0] = fmaf(av, bw.x, acc[p][0]);
+                        acc[p][1] = fmaf(av, bw.y, acc[p][1]);
+                        acc[p][2] = fmaf(av, bw.z, acc[p][2]);
+                        acc[p][3] = fmaf(av, bw.w, acc[p][3]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    const float4 bv = __ldg(reinterpret_cast<const float4 *>(bias + n0 + tc * 4));
+    const int gh = h0 + prow;
+    if (gh < H) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int gw = w0 + pcol0 + p;
+            if (gw < W) {
+                float4 o = make_float4(acc[p][0] + bv.x, acc[p][1] + bv.y, acc[p][2] + bv.z, acc[p][3] + bv.w);
+                if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+                *reinterpret_cast<float4 *>(out + (((size_t)b * H + gh) * W + gw) * Cout + n0 + tc * 4) = o;
+            }
+        }
+    }
+}
+
+// regressor (segnet.py:131,140): 3x3 conv 64->1 + bias on fp32 NHWC; one warp per output pixel
+__global__ void __launch_bounds__(256) regressor_f32_kernel(const float *__restrict__ in, const float *__restrict__ w,
+                                                            const float *__restrict__ bias, float *__restrict__ out,
+                                                            int B, int H, int W) {
+    const int lane = threadIdx.x & 31;
+    const size_t total = (size_t)B * H * W;
+    for (size_t g = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5); g < total; g += (size_t)gridDim.x * 8) {
+        const int wq = (int)(g % W);
+        const int hq = (int)((g / W) % H);
+        const int b = (int)(g / ((size_t)W * H));
+        float s = 0.0f;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int gh = hq + tap / 3 - 1, gw = wq + tap % 3 - 1;
+            if (gh >= 0 && gh < H && gw >= 0 && gw < W) {
+                const float2 v = __ldg(reinterpret_cast<const float2 *>(in + (((size_t)b * H + gh) * W + gw) * 64 + 2 * lane));
+                const float2 ww = __ldg(reinterpret_cast<const float2 *>(w + tap * 64 + 2 * lane));
+                s = fmaf(v.x, ww.x, s);
+                s = fmaf(v.y, ww.y, s);
+            }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+        if (lane == 0) out[g] = s + __ldg(bias);
+    }
+}
+
+// tcgen05 modes: the last conv's epilogue leaves per-pixel, per-tap partial sums of the regressor
+// (regpart [B][H][W][9]); this gathers the 9 shifted partials and adds the bias.
+__global__ void __launch_bounds__(256) regressor_gather_kernel(const float *__restrict__ part, const float *__restrict__ bias,
+                                                               float *__restrict__ out, int B, int H, int W) {
+    const size_t total = (size_t)B * H * W;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int wq = (int)(g % W);
+        const int hq = (int)((g / W) % H);
+        const int b = (int)(g / ((size_t)W * H));
+        float s = 0.0f;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int gh = hq + tap / 3 - 1, gw = wq + tap % 3 - 1;
+            if (gh >= 0 && gh < H && gw >= 0 && gw < W) s += __ldg(part + (((size_t)b * H + gh) * W + gw) * 9 + tap);
+        }
+        out[g] = s + __ldg(bias);
+    }
+}
+
+static inline int ew_blocks(size_t total) {
+    size_t b = (total + 255) / 256;
+    return (int)(b > 148 * 16 ? 148 * 16 : (b < 1 ? 1 : b));
+}
+
+static int conv_f32(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int B, cudaStream_t st) {
+    const ConvLayer &L = ctx->conv[layer];
+    dim3 grid(((in.H + 7) / 8) * ((in.W + 7) / 8), L.cout / 64, B);
+    conv3x3_f32_kernel<<<grid, 256, 0, st>>>(in.f32, L.w32, L.bias, out.f32, in.H, in.W, L.cin, L.cout, 1);
+    GND_LAUNCH_CHECK("conv3x3_f32_kernel");
+    return GND_OK;
+}
+
+int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st) {
+    const bool tc = ctx->cfg.precision != GND_PREC_FP32;
+    int rc;
+#define CONV(l, in, out, fuse)                                                          \
+    do {                                                                                \
+        rc = tc ? tc_conv_run(ctx, l, in, out, B, fuse, st) : conv_f32(ctx, l, in, out, B, st); \
+        if (rc != GND_OK) return rc;                                                    \
+    } while (0)
+    CONV(0, ctx->canvas, ctx->d1a, false);
+    CONV(1, ctx->d1a, ctx->d1b, false);
+    pool_kernel<<<ew_blocks(ctx->p1.elems(B)), 256, 0, st>>>(ctx->d1b, ctx->p1, ctx->idx1, B);
+    GND_LAUNCH_CHECK("pool_kernel");
+    CONV(2, ctx->p1, ctx->d2a, false);
+    CONV(3, ctx->d2a, ctx->d2b, false);
+    pool_mask_kernel<<<ew_blocks(ctx->u2.elems(B)), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
+    GND_LAUNCH_CHECK("pool_mask_kernel");
+    CONV(4, ctx->u2, ctx->u2a, false);
+    CONV(5, ctx->u2a, ctx->u2b, false);
+    unpool_kernel<<<ew_blocks(ctx->u1.elems(B)), 256, 0, st>>>(ctx->u2b, ctx->idx1, ctx->u1, B);
+    GND_LAUNCH_CHECK("unpool_kernel");
+    CONV(6, ctx->u1, ctx->u1a, false);
+    CONV(7, ctx->u1a, ctx->u1b, tc);
+#undef CONV
+    const size_t px = (size_t)B * ctx->ny * ctx->nx;
+    if (tc) {
+        regressor_gather_kernel<<<ew_blocks(px), 256, 0, st>>>(ctx->regpart, ctx->reg_b, height, B, ctx->ny, ctx->nx);
+        GND_LAUNCH_CHECK("regressor_gather_kernel");
+    } else {
+        size_t blocks = (px + 7) / 8;
+        regressor_f32_kernel<<<(int)(blocks > 148 * 16 ? 148 * 16 : blocks), 256, 0, st>>>(ctx->u1b.f32, ctx->reg_w, ctx->reg_b,
+                                                                                          height, B, ctx->ny, ctx->nx);
+        GND_LAUNCH_CHECK("regressor_f32_kernel");
+    }
+    return GND_OK;
+}
+
+}  // namespace gnd

@@ -1,0 +1,403 @@
+// voxelize.cu -- order-exact parallel restatement of the reference's sequential voxelizer.
+//
+// Replaces utils/point_cloud_ops.py:7-53 (_points_to_voxel_reverse_kernel), :55-104 and the wrapper
+// :107-167.  The reference is one sequential loop whose outputs depend on input order three ways:
+//   (1) voxel id   = rank of the cell's FIRST in-range point among all cells' first points (:42-48)
+//   (2) point slot = rank of the point among the points of its cell, kept while < max_points (:49-52)
+//   (3) overflow   = at the first point that would open voxel number max_voxels the loop BREAKS
+//                    (:44-45): that point and every later point is dropped.
+// Parallel formulation (three launches, all bit-exact, no unordered slot assignment anywhere):
+//   vox_rank_kernel    one CTA per (scan, chunk of T consecutive points): all warps compute the float32
+//                      cell of each point (coalesced loads); ONE warp then walks the chunk in input
+//                      order, 32 points per step, ranking equal cells inside the step with match.any and
+//                      across steps with a chunk-local per-cell counter table in shared memory.  Emits
+//                      cell[i], the chunk-local rank, the chunk histogram and atomicMin(first[cell]).
+//   vox_assign_kernel  one CTA per scan: a bitmap over point indices of all `first` values gives every
+//                      occupied cell its voxel id by popcount-prefix (= order of first appearance);
+//                      the cell with rank max_voxels yields the break index; chunk histograms become
+//                      exclusive prefixes; num_points and the CSR offsets of the pillar lists follow.
+//   vox_scatter_kernel one thread per point: slot = chunk prefix + chunk-local rank; kept if
+//                      slot < max_points and index < break index; writes the pillar list (and, for the
+//                      drop-in API, the dense voxels tensor / per-point slot).
+#include "voxelize.cuh"
+#include <limits.h>
+#include <math.h>
+
+namespace gnd {
+
+struct VoxArgs {
+    const float *points;
+    const int32_t *counts;
+    int32_t B;
+    int32_t N;
+    int32_t F;
+    int32_t vec4;          // rows are 16-byte aligned float4
+    float lo[3], vs[3];
+    int32_t grid[3];       // nx ny nz
+    int32_t cells;
+    int32_t K, T;
+    int32_t apply_shift;
+    float z_shift;
+    int32_t max_points, max_voxels, reverse;
+    VoxWs ws;
+    int32_t *coors, *num_points, *voxel_count, *offsets, *list;
+    float *voxels;
+    int32_t *slot;
+};
+
+// utils/point_cloud_ops.py:34-37: c = floor((p - lo) / vs) in IEEE float32 (subtract, then true divide),
+// rejected when c < 0 or c >= grid.  NaN compares false on both of the reference's tests (UB there);
+// here it is rejected.
+__device__ __forceinline__ int axis_cell(float p, float lo, float vs, int grid) {
+    float c = floorf(__fdiv_rn(__fsub_rn(p, lo), vs));
+    if (!(c >= 0.0f) || !(c < (float)grid)) return -1;
+    return (int)c;
+}
+
+__device__ __forceinline__ int point_cell(const VoxArgs &a, const float *row) {
+    float x, y, z;
+    if (a.vec4) {
+        float4 v = __ldg(reinterpret_cast<const float4 *>(row));
+        x = v.x; y = v.y; z = v.z;
+    } else {
+        x = __ldg(row); y = __ldg(row + 1); z = __ldg(row + 2);
+    }
+    if (a.apply_shift) z = __fadd_rn(z, a.z_shift);   // predict_ground.py:104-107
+    int cx = axis_cell(x, a.lo[0], a.vs[0], a.grid[0]);
+    int cy = axis_cell(y, a.lo[1], a.vs[1], a.grid[1]);
+    int cz = axis_cell(z, a.lo[2], a.vs[2], a.grid[2]);
+    if ((cx | cy | cz) < 0) return -1;
+    return (cz * a.grid[1] + cy) * a.grid[0] + cx;
+}
+
+__global__ void __launch_bounds__(256) vox_rank_kernel(const VoxArgs a) {
+    extern __shared__ uint16_t s_tbl[];            // [cells] points of each cell seen so far in this chunk
+    __shared__ int32_t s_cell[VOX_SUB];
+    __shared__ uint16_t s_rank[VOX_SUB];
+    const int b = blockIdx.x / a.K, k = blockIdx.x % a.K;
+    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int start = k * a.T;
+    const int end = min(start + a.T, n);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)b * a.N;
+
+    for (int c = tid; c < a.cells; c += 256) s_tbl[c] = 0;
+    __syncthreads();
+
+    for (int sub = start; sub < end; sub += VOX_SUB) {
+        const int cnt = min(VOX_SUB, end - sub);
+        // phase A: cells of this sub-tile (all warps, coalesced)
+        for (int j = tid; j < cnt; j += 256) {
+            const int64_t gi = base + sub + j;
+            int c = point_cell(a, a.points + gi * a.F);
+            s_cell[j] = c;
+            a.ws.cell[gi] = c;
+        }
+        __syncthreads();
+        // phase B: in-order ranking by one warp
+        if (warp == 0) {
+            int32_t *first = a.ws.first + (int64_t)b * a.cells;
+            for (int j0 = 0; j0 < cnt; j0 += 32) {
+                const int j = j0 + lane;
+                const int c = (j < cnt) ? s_cell[j] : -1;
+                const unsigned act = __ballot_sync(0xffffffffu, c >= 0);
+                if (c >= 0) {
+                    const unsigned peers = __match_any_sync(act, c);
+                    const int leader = __ffs(peers) - 1;
+                    const int pre = __popc(peers & lanemask_lt());
+                    unsigned seen = 0;
+                    if (lane == leader) {
+                        seen = s_tbl[c];
+                        s_tbl[c] = (uint16_t)(seen + __popc(peers));
+                        if (seen == 0) atomicMin(&first[c], sub + j);   // first point of the cell in this chunk
+                    }
+                    seen = __shfl_sync(peers, seen, leader);
+                    s_rank[j] = (uint16_t)(seen + pre);
+                }
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        // phase C: chunk-local ranks out (coalesced)
+        for (int j = tid; j < cnt; j += 256) a.ws.lrank[base + sub + j] = s_rank[j];
+    }
+    __syncthreads();
+    uint32_t *hist = a.ws.hist + ((int64_t)b * a.K + k) * a.cells;
+    for (int c = tid; c < a.cells; c += 256) hist[c] = s_tbl[c];
+}
+
+__global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
+    extern __shared__ uint32_t s_bm[];             // bit i set <=> point i is the first point of a cell
+    __shared__ int s_tpre[1024];
+    __shared__ int s_warp[33];
+    __shared__ int s_cut;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int nW = (n + 31) >> 5;
+    const int32_t *first = a.ws.first + (int64_t)b * a.cells;
+    int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
+    uint32_t *hist = a.ws.hist + (int64_t)b * a.K * a.cells;
+    int32_t *coors = a.coors + (int64_t)b * a.max_voxels * 3;
+    int32_t *num = a.num_points + (int64_t)b * a.max_voxels;
+    int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
+
+    for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
+    if (tid == 0) s_cut = INT_MAX;
+    __syncthreads();
+    for (int c = tid; c < a.cells; c += 1024) {
+        int f = first[c];
+        if (f < n) atomicOr(&s_bm[f >> 5], 1u << (f & 31));
+    }
+    __syncthreads();
+    const int seg = (nW + 1023) / 1024;
+    int local = 0;
+    for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) local += __popc(s_bm[w]);
+    int n_occ;
+    int pre = block_exclusive_scan(local, s_warp, &n_occ);
+    s_tpre[tid] = pre;
+    __syncthreads();
+    const int M = min(n_occ, a.max_voxels);
+
+    // voxel id = number of cells whose first point comes earlier (:42-48); break index (:44-45)
+    const int nx = a.grid[0], ny = a.grid[1];
+    for (int c = tid; c < a.cells; c += 1024) {
+        int f = first[c];
+        int v = -1;
+        if (f < n) {
+            const int w = f >> 5, t = w / seg;
+            int r = s_tpre[t];
+            for (int w2 = t * seg; w2 < w; ++w2) r += __popc(s_bm[w2]);
+            r += __popc(s_bm[w] & ((1u << (f & 31)) - 1u));
+            if (r < a.max_voxels) {
+                v = r;
+                const int cx = c % nx, cy = (c / nx) % ny, cz = c / (nx * ny);
+                if (a.reverse) { coors[v * 3 + 0] = cz; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cx; }
+                else           { coors[v * 3 + 0] = cx; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cz; }
+            } else if (r == a.max_voxels) {
+                s_cut = f;
+            }
+        }
+        vid[c] = v;
+    }
+    __syncthreads();
+    const int cut = s_cut;
+    const int kcut = (cut < n) ? cut / a.T : a.K;
+
+    // chunk histograms -> exclusive prefixes over chunks; points per voxel before truncation
+    for (int c = tid; c < a.cells; c += 1024) {
+        uint32_t run = 0, before_cut = 0;
+        for (int k = 0; k < a.K; ++k) {
+            uint32_t h = hist[(int64_t)k * a.cells + c];
+            hist[(int64_t)k * a.cells + c] = run;
+            if (k == kcut) before_cut = run;
+            run += h;
+        }
+        const int v = vid[c];
+        if (v >= 0) num[v] = (cut < n) ? (int)before_cut : (int)run;
+    }
+    __syncthreads();
+    if (cut < n) {   // overflow: add the points of the break chunk that precede the break index
+        const int32_t *cell = a.ws.cell + (int64_t)b * a.N;
+        for (int j = kcut * a.T + tid; j < cut; j += 1024) {
+            int c = cell[j];
+            if (c >= 0) { int v = vid[c]; if (v >= 0) atomicAdd(&num[v], 1); }
+        }
+        __syncthreads();
+    }
+    // truncate (:49-52) and build the CSR offsets of the pillar point lists
+    const int segM = (M + 1023) / 1024;
+    int lsum = 0;
+    for (int v = tid * segM; v < min((tid + 1) * segM, M); ++v) {
+        int c = min(num[v], a.max_points);
+        num[v] = c;
+        lsum += c;
+    }
+    int S;
+    int run = block_exclusive_scan(lsum, s_warp, &S);
+    for (int v = tid * segM; v < min((tid + 1) * segM, M); ++v) { off[v] = run; run += num[v]; }
+    if (tid == 0) {
+        off[M] = S;
+        a.voxel_count[b] = M;
+        a.ws.cutoff[b] = cut;
+    }
+}
+
+__global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
+    const int64_t total = (int64_t)a.B * a.N;
+    for (int64_t gi = (int64_t)blockIdx.x * 256 + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * 256) {
+        const int b = (int)(gi / a.N), i = (int)(gi - (int64_t)b * a.N);
+        const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+        if (i >= n) { if (a.slot) a.slot[gi] = -1; continue; }
+        const int c = a.ws.cell[gi];
+        int slot = -1;
+        if (c >= 0 && i < a.ws.cutoff[b]) {
+            const int v = a.ws.vid[(int64_t)b * a.cells + c];
+            if (v >= 0) {
+                const int k = i / a.T;
+                const int r = (int)a.ws.lrank[gi] + (int)a.ws.hist[((int64_t)b * a.K + k) * a.cells + c];
+                if (r < a.max_points) {
+                    slot = v * a.max_points + r;
+                    a.list[(int64_t)b * a.N + a.offsets[(int64_t)b * (a.max_voxels + 1) + v] + r] = i;
+                    if (a.voxels) {
+                        const float *src = a.points + gi * a.F;
+                        float *dst = a.voxels + (((int64_t)b * a.max_voxels + v) * a.max_points + r) * a.F;
+                        for (int f = 0; f < a.F; ++f) {
+                            float val = src[f];   // _shift_cloud adds [0,0,h,0] to the first 4 columns
+                            if (a.apply_shift && f < 4) val = __fadd_rn(val, f == 2 ? a.z_shift : 0.0f);
+                            dst[f] = val;
+                        }
+                    }
+                }
+            }
+        }
+        if (a.slot) a.slot[gi] = slot;
+    }
+}
+
+// predict_ground.py:104-107: cloud[:, :4] += float32([0, 0, h, 0]) (so -0.0 becomes +0.0 in every column)
+__global__ void shift_cloud_kernel(float *points, int64_t rows, int F, float h) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < rows)
+        for (int f = 0; f < min(F, 4); ++f) points[i * F + f] = __fadd_rn(points[i * F + f], f == 2 ? h : 0.0f);
+}
+
+// ---- host side ----------------------------------------------------------------------------
+static void host_grid(const gnd_voxel_params *p, int32_t g[3]) {
+    for (int j = 0; j < 3; ++j) {
+        volatile float d = p->coors_range[3 + j] - p->coors_range[j];
+        volatile float q = d / p->voxel_size[j];
+        g[j] = (int32_t)rintf(q);            // np.round == round-half-even (:24-27)
+    }
+}
+
+int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, VoxPlan *plan) {
+    if (!p || !plan) return fail(GND_ERR_INVALID, "null voxel params");
+    if (batch < 1 || n_points < 0) return fail(GND_ERR_INVALID, "batch %d / n_points %lld", batch, (long long)n_points);
+    if (p->num_features < 3) return fail(GND_ERR_INVALID, "points need >= 3 columns, got %d", p->num_features);
+    if (p->max_points < 1 || p->max_voxels < 1) return fail(GND_ERR_INVALID, "max_points/max_voxels must be >= 1");
+    if (p->max_points > 65535) return fail(GND_ERR_UNSUPPORTED, "max_points %d > 65535", p->max_points);
+    for (int j = 0; j < 3; ++j)
+        if (!(p->voxel_size[j] > 0.0f)) return fail(GND_ERR_INVALID, "voxel_size[%d] must be > 0", j);
+    host_grid(p, plan->grid);
+    int64_t cells = 1;
+    for (int j = 0; j < 3; ++j) {
+        if (plan->grid[j] < 1) return fail(GND_ERR_INVALID, "empty voxel grid on axis %d", j);
+        cells *= plan->grid[j];
+    }
+    if (cells > 100000) return fail(GND_ERR_UNSUPPORTED, "voxel grid of %lld cells > 100000 (shared-memory cell table)", (long long)cells);
+    if (n_points > 1600000) return fail(GND_ERR_UNSUPPORTED, "%lld points per scan > 1600000 (shared-memory first-point bitmap)", (long long)n_points);
+    plan->cells = (int32_t)cells;
+    int64_t n = n_points < 1 ? 1 : n_points;
+    int64_t kmin = (n + VOX_MAX_T - 1) / VOX_MAX_T;
+    int64_t kmax = (n + VOX_SUB - 1) / VOX_SUB;
+    int64_t k = (2 * 148 + batch - 1) / batch;              // about two CTAs per SM over the batch
+    if (k > VOX_MAX_K) k = VOX_MAX_K;
+    if (k > kmax) k = kmax;
+    if (k < kmin) k = kmin;
+    int64_t t = (n + k - 1) / k;
+    t = (t + VOX_SUB - 1) / VOX_SUB * VOX_SUB;
+    plan->T = (int32_t)t;
+    plan->K = (int32_t)((n + t - 1) / t);
+    plan->rank_smem = (size_t)plan->cells * sizeof(uint16_t);
+    plan->assign_smem = (size_t)((n_points + 31) / 32 + 1) * sizeof(uint32_t);
+    return GND_OK;
+}
+
+size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out) {
+    Carver c(ws);
+    VoxWs w;
+    size_t bn = (size_t)batch * (size_t)(n_points < 1 ? 1 : n_points);
+    w.cell = c.take<int32_t>(bn);
+    w.lrank = c.take<uint16_t>(bn);
+    w.first = c.take<int32_t>((size_t)batch * plan.cells);
+    w.hist = c.take<uint32_t>((size_t)batch * plan.K * plan.cells);
+    w.vid = c.take<int32_t>((size_t)batch * plan.cells);
+    w.cutoff = c.take<int32_t>((size_t)batch);
+    if (out) *out = w;
+    return c.bytes();
+}
+
+int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+            const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
+            int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,
+            int32_t *point_slot, cudaStream_t stream) {
+    if (!coors || !num_points || !voxel_count || !point_offsets || !point_list)
+        return fail(GND_ERR_INVALID, "voxelizer output pointer is null");
+    if (n_points > 0 && !points) return fail(GND_ERR_INVALID, "points is null");
+    VoxArgs a;
+    a.points = points; a.counts = counts; a.B = batch; a.N = (int32_t)n_points; a.F = p->num_features;
+    a.vec4 = (p->num_features == 4 && ((uintptr_t)points % 16) == 0) ? 1 : 0;
+    for (int j = 0; j < 3; ++j) { a.lo[j] = p->coors_range[j]; a.vs[j] = p->voxel_size[j]; a.grid[j] = plan.grid[j]; }
+    a.cells = plan.cells; a.K = plan.K; a.T = plan.T;
+    a.apply_shift = p->apply_z_shift; a.z_shift = p->z_shift;
+    a.max_points = p->max_points; a.max_voxels = p->max_voxels; a.reverse = p->reverse_index;
+    a.ws = ws; a.coors = coors; a.num_points = num_points; a.voxel_count = voxel_count;
+    a.offsets = point_offsets; a.list = point_list; a.voxels = voxels; a.slot = point_slot;
+
+    GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    GND_CUDA_CHECK(cudaFuncSetAttribute(vox_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+    GND_CUDA_CHECK(cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * plan.cells * sizeof(int32_t), stream));
+    if (n_points > 0) {
+        vox_rank_kernel<<<batch * plan.K, 256, plan.rank_smem, stream>>>(a);
+        GND_LAUNCH_CHECK("vox_rank_kernel");
+    } else {
+        GND_CUDA_CHECK(cudaMemsetAsync(ws.hist, 0, (size_t)batch * plan.K * plan.cells * sizeof(uint32_t), stream));
+    }
+    vox_assign_kernel<<<batch, 1024, plan.assign_smem, stream>>>(a);
+    GND_LAUNCH_CHECK("vox_assign_kernel");
+    if (n_points > 0) {
+        int64_t total = (int64_t)batch * n_points;
+        int blocks = (int)((total + 255) / 256);
+        if (blocks > 148 * 32) blocks = 148 * 32;
+        vox_scatter_kernel<<<blocks, 256, 0, stream>>>(a);
+        GND_LAUNCH_CHECK("vox_scatter_kernel");
+    }
+    return GND_OK;
+}
+
+}  // namespace gnd
+
+// ---- C ABI ----------------------------------------------------------------------------------
+using namespace gnd;
+
+extern "C" int gnd_voxel_grid_size(const gnd_voxel_params *p, int32_t *h_grid_xyz) {
+    if (!p || !h_grid_xyz) return fail(GND_ERR_INVALID, "null argument");
+    host_grid(p, h_grid_xyz);
+    return GND_OK;
+}
+
+extern "C" int gnd_voxel_workspace_bytes(const gnd_voxel_params *p, int32_t batch, int64_t n_points, size_t *h_bytes) {
+    if (!h_bytes) return fail(GND_ERR_INVALID, "null argument");
+    VoxPlan plan;
+    int rc = vox_make_plan(p, batch, n_points, &plan);
+    if (rc != GND_OK) return rc;
+    *h_bytes = vox_carve(plan, batch, n_points, nullptr, nullptr);
+    return GND_OK;
+}
+
+extern "C" int gnd_points_to_voxel(const gnd_voxel_params *p, const float *points, const int32_t *counts,
+                                   int32_t batch, int64_t n_points, void *workspace, size_t workspace_bytes,
+                                   int32_t *coors, int32_t *num_points, int32_t *voxel_count,
+                                   int32_t *point_offsets, int32_t *point_list, float *voxels,
+                                   int32_t *point_slot, void *stream) {
+    g_launches = 0;
+    VoxPlan plan;
+    int rc = vox_make_plan(p, batch, n_points, &plan);
+    if (rc != GND_OK) return rc;
+    VoxWs ws;
+    size_t need = vox_carve(plan, batch, n_points, workspace, &ws);
+    if (!workspace || workspace_bytes < need)
+        return fail(GND_ERR_WORKSPACE, "voxel workspace: need %zu bytes, got %zu", need, workspace_bytes);
+    return vox_run(p, plan, ws, points, counts, batch, n_points, coors, num_points, voxel_count,
+                   point_offsets, point_list, voxels, point_slot, (cudaStream_t)stream);
+}
+
+extern "C" int gnd_shift_cloud(float *points, int64_t n_rows, int32_t num_features, float height, void *stream) {
+    g_launches = 0;
+    if (n_rows < 0 || num_features < 3) return fail(GND_ERR_INVALID, "bad shape");
+    if (n_rows == 0) return GND_OK;
+    if (!points) return fail(GND_ERR_INVALID, "points is null");
+    shift_cloud_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(points, n_rows, num_features, height);
+    GND_LAUNCH_CHECK("shift_cloud_kernel");
+    return GND_OK;
+}

@@ -1,0 +1,37 @@
+// voxelize.cuh -- internal interface of the order-exact parallel voxelizer (see voxelize.cu).
+#pragma once
+#include "common.cuh"
+
+namespace gnd {
+
+constexpr int VOX_SUB = 2048;        // points ranked per sub-tile of a chunk
+constexpr int VOX_MAX_T = 61440;     // chunk size limit: chunk-local counts are uint16
+constexpr int VOX_MAX_K = 64;        // chunks per scan
+
+struct VoxPlan {
+    int32_t grid[3];     // nx, ny, nz   (utils/point_cloud_ops.py:24-27)
+    int32_t cells;       // nx*ny*nz
+    int32_t K;           // chunks per scan
+    int32_t T;           // points per chunk (multiple of VOX_SUB)
+    size_t rank_smem;    // dynamic smem of the rank kernel
+    size_t assign_smem;  // dynamic smem of the assign kernel
+};
+
+// scratch carved from the caller's workspace
+struct VoxWs {
+    int32_t *cell;       // [B][N]      linear cell of every point, -1 if rejected
+    uint16_t *lrank;     // [B][N]      rank of the point among its cell's points inside its chunk
+    int32_t *first;      // [B][cells]  index of the first point of the cell (INT_MAX-like if none)
+    uint32_t *hist;      // [B][K][cells] chunk histogram -> exclusive prefix over chunks (in place)
+    int32_t *vid;        // [B][cells]  voxel id of the cell, -1 if none
+    int32_t *cutoff;     // [B]         first dropped index when max_voxels overflows, else INT_MAX
+};
+
+int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, VoxPlan *plan);
+size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out);
+int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+            const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
+            int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,
+            int32_t *point_slot, cudaStream_t stream);
+
+}  // namespace gnd

@@ -1,0 +1,318 @@
+"""Drop-in for the reference's ``model.py`` (GroundEstimatorNet) plus the fused device pipeline.
+
+``GroundEstimatorNet(cfg)`` keeps the reference's surface (model.py:13-42):
+  * an ``nn.Module`` whose ``state_dict()`` has exactly the reference's keys and shapes, so
+    ``model.load_state_dict(checkpoint['state_dict'])`` (predict_ground.py:196, ros_node.py:223) works;
+  * sub-module attribute names ``voxel_feature_extractor`` / ``middle_feature_extractor`` /
+    ``encoder_decoder`` (model.py:19,31,34);
+  * ``forward(voxels [M,P,F], coors [M,4] (b,z,y,x), num_points [M]) -> torch.squeeze([B,1,ny,nx])``,
+    with ``cfg.batch_size`` read at every call (model.py:36-42).
+The torch modules below are parameter containers only: the arithmetic runs in libgndnet_b200.so.
+BatchNorm is evaluated with running statistics (eval mode, as the deployed node does,
+ros_node.py:227); the kernels fold it into the conv / linear weights at load time.
+
+``GroundEstimatorNet.infer(points)`` is the additive fused entry: raw scans in,
+height maps and per-point labels out, no dense ``voxels`` tensor and no host round trip.
+"""
+import ctypes
+import warnings
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class _Empty(nn.Module):
+    """torchplus.nn.Empty (torchplus/nn/modules/common.py:7-16): parameter-free placeholder."""
+
+    def forward(self, *args):
+        return args[0] if len(args) == 1 else args
+
+
+class PFNLayer(nn.Module):
+    """Parameter layout of modules/pointpillars.py:19-50."""
+
+    def __init__(self, in_channels, out_channels, use_norm=True, last_layer=True):
+        super().__init__()
+        if use_norm:
+            self.linear = nn.Linear(in_channels, out_channels, bias=False)
+            self.norm = nn.BatchNorm1d(out_channels, eps=1e-3, momentum=0.01)
+        else:
+            self.linear = nn.Linear(in_channels, out_channels, bias=True)
+            self.norm = _Empty()
+
+
+class PillarFeatureNet(nn.Module):
+    """Parameter layout of modules/pointpillars.py:68-113."""
+
+    def __init__(self, num_input_features=4, use_norm=True, num_filters=(64,), with_distance=False,
+                 voxel_size=(0.2, 0.2, 4), pc_range=(0, -40, -3, 70.4, 40, 1)):
+        super().__init__()
+        if list(num_filters) != [64]:
+            raise NotImplementedError("vfe_filters must be [64] (every shipped config); got %r" % (num_filters,))
+        n_in = num_input_features + 5 + (1 if with_distance else 0)
+        self.pfn_layers = nn.ModuleList([PFNLayer(n_in, 64, use_norm, last_layer=True)])
+
+
+class PointPillarsScatter(nn.Module):
+    """modules/pointpillars.py:149-166: no parameters; the scatter is fused into the PFN kernel."""
+
+    def __init__(self, output_shape, num_input_features=64):
+        super().__init__()
+        self.output_shape = output_shape
+        self.ny, self.nx = output_shape[2], output_shape[3]
+        self.nchannels = num_input_features
+
+
+class _ConvBNReLU(nn.Module):
+    """conv2DBatchNormRelu (modules/segnet.py:11-44)."""
+
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.cbr_unit = nn.Sequential(nn.Conv2d(cin, cout, 3, 1, 1, bias=True), nn.BatchNorm2d(cout),
+                                      nn.ReLU(inplace=True))
+
+
+class _Block2(nn.Module):
+    def __init__(self, c1_in, c1_out, c2_out):
+        super().__init__()
+        self.conv1 = _ConvBNReLU(c1_in, c1_out)
+        self.conv2 = _ConvBNReLU(c1_out, c2_out)
+
+
+class SegnetGndEst(nn.Module):
+    """Parameter layout of segnetGndEst (modules/segnet.py:118-131)."""
+
+    def __init__(self, in_channels=64):
+        super().__init__()
+        self.down1 = _Block2(in_channels, 128, 128)     # segnetDown2(64, 128)
+        self.down2 = _Block2(128, 256, 256)             # segnetDown2(128, 256)
+        self.up2 = _Block2(256, 256, 128)               # segnetUp2(256, 128)
+        self.up1 = _Block2(128, 128, 64)                # segnetUp2(128, 64)
+        self.regressor = nn.Conv2d(64, 1, kernel_size=3, padding=1)
+
+
+class GroundEstimatorNet(nn.Module):
+    def __init__(self, cfg, precision=None):
+        super().__init__()
+        self.cfg = cfg
+        self.precision = precision or getattr(cfg, "precision", "fp32")
+        if self.precision not in _lib.PRECISIONS:
+            raise ValueError("precision must be one of %s" % sorted(_lib.PRECISIONS))
+        self.voxel_feature_extractor = PillarFeatureNet(
+            num_input_features=cfg.input_features, use_norm=cfg.use_norm, num_filters=cfg.vfe_filters,
+            with_distance=cfg.with_distance, voxel_size=cfg.voxel_size, pc_range=cfg.pc_range)
+        grid = (np.asarray(cfg.pc_range[3:]) - np.asarray(cfg.pc_range[:3])) / np.asarray(cfg.voxel_size)
+        grid = np.round(grid).astype(np.int64)                       # model.py:26-28
+        dense_shape = [1] + grid[::-1].tolist() + [cfg.vfe_filters[-1]]
+        self.middle_feature_extractor = PointPillarsScatter(output_shape=dense_shape,
+                                                            num_input_features=cfg.vfe_filters[-1])
+        self.encoder_decoder = SegnetGndEst(in_channels=64)
+        self.nz, self.ny, self.nx = int(grid[2]), int(grid[1]), int(grid[0])
+        self._ctx = None
+        self._ctx_device = None
+        self._weights_version = None
+        self._ws = None
+        self._bound = None
+        self._warned_train = False
+        self._tensors = None
+        self.launches = 0
+
+    # ------------------------------------------------------------------ context management
+    def _config_struct(self):
+        cfg = self.cfg
+        c = _lib.Config()
+        for j in range(6):
+            c.pc_range[j] = float(np.float32(cfg.pc_range[j]))
+            c.pc_range_f64[j] = float(cfg.pc_range[j])
+        for j in range(3):
+            c.voxel_size[j] = float(np.float32(cfg.voxel_size[j]))
+            c.voxel_size_f64[j] = float(cfg.voxel_size[j])
+        gr = getattr(cfg, "grid_range", [cfg.pc_range[0], cfg.pc_range[1], cfg.pc_range[3], cfg.pc_range[4]])
+        for j in range(4):
+            c.grid_range[j] = float(gr[j])
+        c.lidar_height = float(np.float32(getattr(cfg, "lidar_height", 0.0)))
+        c.max_points_voxel = int(getattr(cfg, "max_points_voxel", 100))
+        c.max_voxels = int(getattr(cfg, "max_voxels", self.nx * self.ny * self.nz))
+        c.input_features = int(cfg.input_features)
+        c.use_norm = 1 if cfg.use_norm else 0
+        c.with_distance = 1 if cfg.with_distance else 0
+        c.precision = _lib.PRECISIONS[self.precision]
+        return c
+
+    def _device(self):
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("gndnet_b200.GroundEstimatorNet runs on CUDA only -- call .cuda() first "
+                               "(there is no CPU path)")
+        return dev
+
+    def _params_version(self):
+        # Parameter / buffer objects survive .cuda() and load_state_dict(); in-place updates bump _version
+        if self._tensors is None:
+            self._tensors = list(self.state_dict(keep_vars=True).values())
+        return tuple(t._version for t in self._tensors)
+
+    def _ensure_ctx(self):
+        dev = self._device()
+        L = _lib.lib()
+        if self._ctx is None or self._ctx_device != dev:
+            self.release()
+            handle = ctypes.c_void_p()
+            c = self._config_struct()
+            _lib.check(L.gnd_create(ctypes.byref(c), dev.index if dev.index is not None else torch.cuda.current_device(),
+                                    ctypes.byref(handle)), "gnd_create")
+            self._ctx, self._ctx_device = handle, dev
+            self._weights_version = None
+            self._bound = None
+            self._tensors = None
+        ver = self._params_version()
+        if ver != self._weights_version:
+            self._upload_weights()
+            self._weights_version = ver
+        return self._ctx
+
+    def _upload_weights(self):
+        """gnd_load_weights: the C side of load_state_dict (BatchNorm folding + repack)."""
+        L = _lib.lib()
+        sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()
+              if not k.endswith("num_batches_tracked")}
+        arr = (_lib.Weight * len(sd))()
+        keep = []
+        for i, (k, v) in enumerate(sd.items()):
+            name = k.encode()
+            keep.append((name, v))
+            arr[i].name = name
+            arr[i].h_data = ctypes.cast(v.data_ptr(), ctypes.POINTER(ctypes.c_float))
+            arr[i].numel = v.numel()
+        with torch.cuda.device(self._ctx_device):
+            torch.cuda.synchronize()
+            _lib.check(L.gnd_load_weights(self._ctx, arr, len(sd)), "gnd_load_weights")
+
+    def _ensure_workspace(self, batch, n_points):
+        L = _lib.lib()
+        if self._bound is not None and self._bound[0] >= batch and self._bound[1] == n_points:
+            return
+        need = ctypes.c_size_t()
+        _lib.check(L.gnd_workspace_bytes(self._ctx, batch, n_points, ctypes.byref(need)), "gnd_workspace_bytes")
+        with torch.cuda.device(self._ctx_device):
+            torch.cuda.synchronize()
+            self._ws = None
+            ws = torch.empty(need.value + 1024, dtype=torch.uint8, device=self._ctx_device)
+            off = (-ws.data_ptr()) % 1024
+            self._ws = ws
+            _lib.check(L.gnd_bind_workspace(self._ctx, ctypes.c_void_p(ws.data_ptr() + off), need.value, batch, n_points),
+                       "gnd_bind_workspace")
+        self._bound = (batch, n_points)
+
+    def release(self):
+        if self._ctx is not None:
+            _lib.lib().gnd_destroy(self._ctx)
+        self._ctx, self._ws, self._bound = None, None, None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+    def _check_mode(self):
+        if self.training and not self._warned_train:
+            warnings.warn("gndnet_b200 evaluates BatchNorm with running statistics (eval mode); the module is in "
+                          "training mode -- call .eval() (predict_ground.py omits it, ros_node.py:227 does not)")
+            self._warned_train = True
+
+    def buffer(self, name, dtype, shape=None):
+        """Test / profiling hook: a workspace buffer as a tensor view (gnd_get_buffer)."""
+        L = _lib.lib()
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _lib.check(L.gnd_get_buffer(self._ctx, name.encode(), ctypes.byref(p), ctypes.byref(n)), "gnd_get_buffer")
+        off = p.value - self._ws.data_ptr()
+        t = self._ws[off:off + n.value].view(dtype)
+        return t.view(shape) if shape is not None else t
+
+    def last_launch_count(self):
+        return int(_lib.lib().gnd_last_launch_count(self._ctx)) if self._ctx is not None else 0
+
+    # ------------------------------------------------------------------ reference API
+    def forward(self, voxels, coors, num_points):
+        """model.py:36-42 on the drop-in tensors."""
+        self._check_mode()
+        ctx = self._ensure_ctx()
+        L = _lib.lib()
+        B = int(self.cfg.batch_size)
+        dev = self._ctx_device
+        voxels = voxels.to(dev, torch.float32).contiguous()
+        coors = coors.to(dev, torch.float32).contiguous()
+        num_points = num_points.to(dev, torch.float32).contiguous()
+        if voxels.dim() != 3 or voxels.shape[2] != self.cfg.input_features:
+            raise ValueError("voxels must be [M, P, %d]" % self.cfg.input_features)
+        if voxels.shape[1] != int(getattr(self.cfg, "max_points_voxel", voxels.shape[1])):
+            raise ValueError("voxels.shape[1] must equal cfg.max_points_voxel")
+        if coors.shape != (voxels.shape[0], 4) or num_points.shape != (voxels.shape[0],):
+            raise ValueError("coors must be [M, 4] (b, z, y, x) and num_points [M]")
+        self._ensure_workspace(B, self._bound[1] if self._bound else 0)
+        with torch.cuda.device(dev):
+            height = torch.empty((B, 1, self.ny, self.nx), dtype=torch.float32, device=dev)
+            st = _lib.stream_ptr()
+            _lib.check(L.gnd_pfn_scatter_dense(ctx, _lib.ptr(voxels), _lib.ptr(coors), _lib.ptr(num_points),
+                                               voxels.shape[0], B, st), "gnd_pfn_scatter_dense")
+            n1 = self.last_launch_count()
+            _lib.check(L.gnd_segnet(ctx, B, _lib.ptr(height), st), "gnd_segnet")
+            self.launches = n1 + self.last_launch_count()
+        return torch.squeeze(height)
+
+    # ------------------------------------------------------------------ fused path
+    def infer(self, points, threshold=0.08, counts=None, labels="int8", out=None):
+        """Raw scans -> (height [B, ny, nx] float32, labels [B, N]).
+
+        ``points``: float32 CUDA tensor [B, N, F] (or [N, F]) in the sensor frame; the +lidar_height z-shift
+        (predict_ground.py:112), voxelization, pillar encoding, scatter, segnet and the point labelling
+        against ``cfg.grid_range`` (predict_ground.py:168) all run on the device, enqueued back to back.
+        ``labels``: "int8", "float64" (the reference's dtype) or None.  ``out``: optional (height, labels)
+        tensors to write into.
+        """
+        self._check_mode()
+        ctx = self._ensure_ctx()
+        L = _lib.lib()
+        single = points.dim() == 2
+        if single:
+            points = points.unsqueeze(0)
+        if not (points.is_cuda and points.dtype == torch.float32 and points.is_contiguous()
+                and points.dim() == 3 and points.shape[2] == self.cfg.input_features):
+            raise TypeError("points must be a contiguous float32 CUDA tensor [B, N, %d]" % self.cfg.input_features)
+        B, N, _ = points.shape
+        self._ensure_workspace(B, N)
+        dev = self._ctx_device
+        with torch.cuda.device(dev):
+            if out is not None:
+                height, lab = out
+            else:
+                height = torch.empty((B, self.ny, self.nx), dtype=torch.float32, device=dev)
+                lab = None
+                if labels == "int8":
+                    lab = torch.empty((B, N), dtype=torch.int8, device=dev)
+                elif labels == "float64":
+                    lab = torch.empty((B, N), dtype=torch.float64, device=dev)
+            l8 = lab if (lab is not None and lab.dtype == torch.int8) else None
+            l64 = lab if (lab is not None and lab.dtype == torch.float64) else None
+            _lib.check(L.gnd_infer(ctx, _lib.ptr(points), _lib.ptr(counts), B, N, float(threshold), _lib.ptr(height),
+                                   _lib.ptr(l8), _lib.ptr(l64), _lib.stream_ptr()), "gnd_infer")
+            self.launches = self.last_launch_count()
+        if single:
+            return height[0], (lab[0] if lab is not None else None)
+        return height, lab
+
+    def pillars(self, batch):
+        """Voxelizer outputs of the last infer() as tensors (views of the workspace)."""
+        mv = int(getattr(self.cfg, "max_voxels", self.nx * self.ny * self.nz))
+        Bb, N = self._bound
+        return dict(
+            coors=self.buffer("coors", torch.int32, (Bb, mv, 3))[:batch],
+            num_points=self.buffer("num_points", torch.int32, (Bb, mv))[:batch],
+            voxel_count=self.buffer("voxel_count", torch.int32, (Bb,))[:batch],
+            point_offsets=self.buffer("point_offsets", torch.int32, (Bb, mv + 1))[:batch],
+            point_list=self.buffer("point_list", torch.int32, (Bb, max(N, 1)))[:batch],
+        )

@@ -1,0 +1,208 @@
+/*
+ * gndnet_b200.h -- C ABI of libgndnet_b200.so (sm_100a CUDA kernels for the GndNet
+ * inference hot path: voxelize -> pillar-encode -> scatter -> segnet -> point labels).
+ *
+ * Boundary rules:
+ *   - extern "C", plain pointers and sizes, no torch / C++ types in any signature;
+ *   - every data pointer is a DEVICE pointer owned by the caller unless its name starts
+ *     with h_ (host); every call takes an explicit cudaStream_t (passed as void*);
+ *   - calls only enqueue work: no allocation, no synchronisation, CUDA-graph capturable
+ *     (gnd_create / gnd_load_weights / gnd_bind_workspace are the set-up exceptions);
+ *   - every call returns an int status (GND_OK or a negative gnd_status); the message
+ *     of the last failure on the calling thread is gnd_last_error_string().
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * pem-gini/GndNet repo root).  The reference has no FFI of its own -- it is pure Python
+ * (numba + torch) -- so the reference-side binding is a ctypes stub; see INTEGRATION.md.
+ */
+#ifndef GNDNET_B200_H
+#define GNDNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GND_API __attribute__((visibility("default")))
+#else
+#define GND_API
+#endif
+
+typedef enum gnd_status {
+    GND_OK = 0,
+    GND_ERR_INVALID = -1,      /* bad argument */
+    GND_ERR_WORKSPACE = -2,    /* workspace missing or too small */
+    GND_ERR_CUDA = -3,         /* a CUDA runtime / driver call failed */
+    GND_ERR_UNSUPPORTED = -4,  /* outside the supported envelope (see DESIGN.md limits) */
+    GND_ERR_STATE = -5         /* weights not loaded / workspace not bound */
+} gnd_status;
+
+/* arithmetic used by the segnet convolutions */
+typedef enum gnd_precision {
+    GND_PREC_FP32 = 0,   /* CUDA-core fp32 implicit GEMM (strict mode, 1e-3 m bar)          */
+    GND_PREC_MIXED = 1,  /* tcgen05: split-fp16 (hi+lo, 3 products) encoder, fp16 decoder    */
+    GND_PREC_SPLIT = 2   /* tcgen05: split-fp16 everywhere (fp32-class accuracy)             */
+} gnd_precision;
+
+GND_API const char *gnd_last_error_string(void);
+GND_API int gnd_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Voxelizer.  Replaces utils/point_cloud_ops.py:107-167 points_to_voxel and the numba loops
+ * :7-53 (_points_to_voxel_reverse_kernel) / :55-104 (_points_to_voxel_kernel), batched over
+ * independent scans, optionally fused with the caller's z-shift (predict_ground.py:104-107).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct gnd_voxel_params {
+    float voxel_size[3];     /* xyz, already in the points' dtype (float32), :138-139        */
+    float coors_range[6];    /* xyzxyz min/max, float32, :140-141                             */
+    int32_t max_points;      /* per voxel, :50                                                */
+    int32_t max_voxels;      /* per scan, :44-45 (break on overflow)                          */
+    int32_t reverse_index;   /* 1: coors are (z,y,x) (:38), 0: (x,y,z) (:86)                  */
+    int32_t num_features;    /* columns of the point array (row stride in floats), >= 3       */
+    int32_t apply_z_shift;   /* 1: use z + z_shift (float32 add) as the point's z everywhere  */
+    float z_shift;           /* cfg.lidar_height                                              */
+} gnd_voxel_params;
+
+/* grid = round((hi - lo) / vs) in float32 (:24-27, :142-143); h_grid_xyz[3] on the host. */
+GND_API int gnd_voxel_grid_size(const gnd_voxel_params *p, int32_t *h_grid_xyz);
+
+/* Bytes of scratch gnd_points_to_voxel needs for `batch` scans of at most n_points each. */
+GND_API int gnd_voxel_workspace_bytes(const gnd_voxel_params *p, int32_t batch, int64_t n_points,
+                                      size_t *h_bytes);
+
+/*
+ * points        [batch][n_points][num_features] float32
+ * counts        [batch] int32 real points per scan (<= n_points), or NULL for "all n_points"
+ * coors         [batch][max_voxels][3] int32     out: first voxel_count[b] rows valid
+ * num_points    [batch][max_voxels]    int32     out
+ * voxel_count   [batch]                int32     out: M per scan (the reference's voxel_num)
+ * point_offsets [batch][max_voxels+1]  int32     out: CSR offsets into point_list (row M = kept points)
+ * point_list    [batch][n_points]      int32     out: kept point indices, voxel-major, input order inside
+ * voxels        [batch][max_voxels][max_points][num_features] float32, ZERO-FILLED by the caller
+ *               (:149-150), or NULL: the fused path never materialises it
+ * point_slot    [batch][n_points] int32, or NULL: voxel*max_points + slot the point went to, -1 if dropped
+ * NaN coordinates are undefined behaviour in the reference; here such points are dropped.
+ */
+GND_API int gnd_points_to_voxel(const gnd_voxel_params *p, const float *points, const int32_t *counts,
+                                int32_t batch, int64_t n_points, void *workspace, size_t workspace_bytes,
+                                int32_t *coors, int32_t *num_points, int32_t *voxel_count,
+                                int32_t *point_offsets, int32_t *point_list, float *voxels,
+                                int32_t *point_slot, void *stream);
+
+/* predict_ground.py:104-107 _shift_cloud / utils/utils.py:137-139: cloud[:, 2] += height in place. */
+GND_API int gnd_shift_cloud(float *points, int64_t n_rows, int32_t num_features, float height, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Per-point labelling.  Replaces utils/utils.py:198-220 segment_cloud and :222-248
+ * segment_cloud_noground.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct gnd_segment_params {
+    double grid_lo[2];       /* grid_size[0], grid_size[1] as float64 (:204)                  */
+    double voxel_size;       /* Python scalar -> float64 division (:205)                      */
+    double threshold;        /* :214                                                          */
+    int32_t map_nx, map_ny;  /* elevation_map.shape: the map is indexed [x, y] (:214)         */
+    int64_t map_sx, map_sy;  /* element strides of that [x, y] view (callers pass pred.T)      */
+    int64_t map_batch_stride;/* elements between consecutive scans' maps                      */
+    int32_t num_features;    /* row stride of points in floats, >= 3                          */
+    int32_t apply_z_shift;   /* 1: compare z + z_shift (fused path: points are the raw scan)  */
+    float z_shift;
+    int32_t mutate_points;   /* 1: write the shifted x,y back like the reference does (:204)  */
+} gnd_segment_params;
+
+/*
+ * points      [batch][n_points][num_features] float32 (columns 0,1 rewritten if mutate_points)
+ * counts      [batch] int32 or NULL
+ * elevation   float32 height maps
+ * labels_f64  [batch][n_points] float64 in {1,0,-1} (the reference's return dtype), or NULL
+ * labels_i8   [batch][n_points] int8, or NULL
+ */
+GND_API int gnd_segment_cloud(const gnd_segment_params *p, float *points, const int32_t *counts,
+                              int32_t batch, int64_t n_points, const float *elevation,
+                              double *labels_f64, int8_t *labels_i8, void *stream);
+
+GND_API int gnd_compact_workspace_bytes(int64_t n_points, size_t *h_bytes);
+/*
+ * segment_cloud_noground's obstacle compaction (:242-243, :248), one scan: rows of points_obstacle
+ * [n_points][obstacle_features] whose label is 1 are moved to the front in input order (stable).
+ * out_obstacle may alias nothing (separate output buffer); obstacle_count is a device int32.
+ */
+GND_API int gnd_compact_obstacles(const int8_t *labels_i8, const float *points_obstacle, int64_t n_points,
+                                  int32_t obstacle_features, void *workspace, size_t workspace_bytes,
+                                  float *out_obstacle, int32_t *obstacle_count, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Model context.  Replaces model.py:13-42 GroundEstimatorNet (+ modules/pointpillars.py,
+ * modules/segnet.py) in eval mode, and predict_ground.py:110-121,165-168 InferGround +
+ * segmentation as one enqueue.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct gnd_ctx gnd_ctx;
+
+typedef struct gnd_config {
+    float pc_range[6];          /* cfg.pc_range                                               */
+    float voxel_size[3];        /* cfg.voxel_size                                             */
+    double pc_range_f64[6];     /* same, as the Python floats the model's offsets are made of */
+    double voxel_size_f64[3];
+    double grid_range[4];       /* cfg.grid_range (segmentation frame)                        */
+    float lidar_height;         /* cfg.lidar_height                                           */
+    int32_t max_points_voxel;   /* cfg.max_points_voxel                                       */
+    int32_t max_voxels;         /* cfg.max_voxels                                             */
+    int32_t input_features;     /* cfg.input_features (3 or 4)                                */
+    int32_t use_norm;           /* cfg.use_norm: Linear(no bias)+BatchNorm1d vs Linear(bias)   */
+    int32_t with_distance;      /* cfg.with_distance                                          */
+    int32_t precision;          /* gnd_precision                                              */
+} gnd_config;
+
+GND_API int gnd_create(const gnd_config *cfg, int32_t device, gnd_ctx **out);
+GND_API void gnd_destroy(gnd_ctx *ctx);
+
+/* One state_dict entry: the reference's key, float32 HOST data, element count. */
+typedef struct gnd_weight {
+    const char *name;
+    const float *h_data;
+    int64_t numel;
+} gnd_weight;
+
+/* model.load_state_dict(checkpoint['state_dict']) (predict_ground.py:196): folds BatchNorm
+ * (eval mode), repacks to the kernels' layouts and uploads.  Synchronous set-up call. */
+GND_API int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n_entries);
+
+GND_API int gnd_workspace_bytes(const gnd_ctx *ctx, int32_t batch, int64_t n_points, size_t *h_bytes);
+/* Carves the caller's device buffer for (batch, n_points) and builds the TMA descriptors. */
+GND_API int gnd_bind_workspace(gnd_ctx *ctx, void *workspace, size_t bytes, int32_t batch, int64_t n_points);
+
+GND_API int gnd_grid_shape(const gnd_ctx *ctx, int32_t *h_nz_ny_nx);
+
+/* Stage 1 (fused path): voxelize `batch` raw scans (z-shift fused) into the bound workspace. */
+GND_API int gnd_voxelize(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
+                         int64_t n_points, void *stream);
+/* Stage 2: PillarFeatureNet + PointPillarsScatter (pointpillars.py:115-146, :168-199) from the
+ * workspace's pillar lists straight into the BEV canvas. */
+GND_API int gnd_pfn_scatter(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_points, void *stream);
+/* Stage 2, drop-in tensors: forward(voxels [M,P,F], coors [M,4] float (b,z,y,x), num_points [M] float)
+ * as model.py:36-42 receives them. */
+GND_API int gnd_pfn_scatter_dense(gnd_ctx *ctx, const float *voxels, const float *coors4,
+                                  const float *num_points, int64_t n_pillars, int32_t batch, void *stream);
+/* Stage 3: segnetGndEst.forward (segnet.py:133-142) canvas -> height [batch][ny][nx] float32. */
+GND_API int gnd_segnet(gnd_ctx *ctx, int32_t batch, float *height, void *stream);
+/* Stage 4: labels for the raw scans against `height` (z-shift fused; grid_range frame). */
+GND_API int gnd_segment(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
+                        int64_t n_points, const float *height, double threshold, int8_t *labels_i8,
+                        double *labels_f64, void *stream);
+/* Stages 1-4 back to back on `stream`. */
+GND_API int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
+                      int64_t n_points, double threshold, float *height, int8_t *labels_i8,
+                      double *labels_f64, void *stream);
+
+/* Test / profiling hook: device pointer + bytes of a named workspace buffer ("canvas", "coors",
+ * "num_points", "voxel_count", "point_offsets", "point_list", "act:<stage>", ...). */
+GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *bytes);
+/* Number of kernels the last gnd_* call on this ctx enqueued (bench.py's gpu_launches). */
+GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNDNET_B200_H */

@@ -1,0 +1,152 @@
+"""GPU parity: PillarFeatureNet + scatter + segnet + end-to-end inference against the CPU oracle
+(oracle/model_ref.py, pinned to the reference) and the reference's golden height maps.
+
+Tolerances (BASELINE.json north_star): height within 1e-3 m for fp32 arithmetic, 5e-3 m when the
+convolutions run on 16-bit tensor-core operands; labels equal on >= 99.9 % of points."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_ops, model_ref, synth
+from tests import cases, helpers
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 1e-3, "split": 1e-3, "mixed": 5e-3}
+
+
+def _available_precisions():
+    return ["fp32"]
+
+
+def _run_case(cfgname, scans, overrides, precision, device):
+    cfg = synth.make_cfg(cfgname, batch_size=len(scans), **overrides)
+    model, sd = helpers.load_model(cfg, cfgname, precision, device)
+    raws = [cases.load_case(s)[1] for s in scans]
+    v, c, n, shifted = helpers.oracle_pillars(cfg, raws)
+    ref, st = model_ref.forward(sd, cfg, v, c, n, return_stages=True)
+    return cfg, model, sd, raws, (v, c, n), shifted, ref, st
+
+
+MODEL_CASES = [("camera", ["small_camera"], {}, "camera__small_camera"),
+               ("kitti", ["small_kitti"], dict(use_norm=True), "kitti__small_kitti_norm"),
+               ("kitti", ["hdl64_s0"], {}, "kitti__hdl64_s0"),
+               ("kitti", ["hdl64_s1", "uniform_s0", "real_000000"], {}, "kitti__hdl64_s1_uniform_s0_real_000000")]
+
+
+@pytest.mark.parametrize("precision", _available_precisions())
+@pytest.mark.parametrize("cfgname,scans,overrides,key", MODEL_CASES)
+def test_forward_dropin_matches_oracle_and_golden(cfgname, scans, overrides, key, precision, cuda):
+    """model(voxels, coors, num_points) exactly as predict_ground.py:115-120 / training.py:138-147 call it."""
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, scans, overrides, precision, cuda)
+    with torch.no_grad():
+        out = model(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
+    assert out.shape == ref.shape, "torch.squeeze semantics (model.py:42)"
+    B = len(scans)
+    # stage check: the BEV canvas the PFN kernel wrote
+    if precision == "fp32":
+        canvas = model.buffer("canvas", torch.float32, (B, model.ny, model.nx, 64)).permute(0, 3, 1, 2).cpu()
+    else:
+        canvas = (model.buffer("canvas.hi", torch.float16, (B, model.ny, model.nx, 64)).float()
+                  + model.buffer("canvas.lo", torch.float16, (B, model.ny, model.nx, 64)).float()).permute(0, 3, 1, 2).cpu()
+    dc = (canvas - st["canvas"]).abs().max().item()
+    assert dc <= 2e-5 * max(1.0, st["canvas"].abs().max().item()), "canvas differs by %g" % dc
+    stable_max, frac_masked, overall = helpers.compare_heights(out, ref, st, TOL[precision])
+    print("%s %s: max|dh| stable=%.3g overall=%.3g masked=%.3f%% canvas=%.3g" % (key, precision, stable_max, overall, 100 * frac_masked, dc))
+    assert frac_masked < 0.05
+    assert stable_max <= TOL[precision]
+    with np.load(cases.GOLDEN + "/model_heights.npz") as z:
+        gold = torch.from_numpy(z[key])
+    stable_max_g, _, _ = helpers.compare_heights(out, gold, st, TOL[precision])
+    assert stable_max_g <= TOL[precision], "differs from the reference's own output by %g" % stable_max_g
+
+
+@pytest.mark.parametrize("precision", _available_precisions())
+def test_fp32_stage_by_stage(precision, cuda):
+    """Every intermediate activation of the fp32 path against the oracle's (pool / unpool semantics included)."""
+    if precision != "fp32":
+        pytest.skip("stage buffers are fp32 only in fp32 mode")
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case("camera", ["small_camera"], {}, precision, cuda)
+    with torch.no_grad():
+        model(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
+    H, W = model.ny, model.nx
+    shapes = dict(d1a=(H, W, 128), d1b=(H, W, 128), p1=(H // 2, W // 2, 128), d2a=(H // 2, W // 2, 256),
+                  d2b=(H // 2, W // 2, 256), u2=(H // 2, W // 2, 256), u2a=(H // 2, W // 2, 256),
+                  u2b=(H // 2, W // 2, 128), u1=(H, W, 128), u1a=(H, W, 128), u1b=(H, W, 64))
+    for name, (h, w, ch) in shapes.items():
+        got = model.buffer(name, torch.float32, (1, h, w, ch)).permute(0, 3, 1, 2).cpu()
+        exp = st[name]
+        d = (got - exp).abs()
+        scale = max(1.0, exp.abs().max().item())
+        bad = (d > 1e-4 * scale).float().mean().item()
+        print("%-4s max|d|=%.3g  frac>1e-4=%.4f" % (name, d.max().item(), bad))
+        assert bad < 0.002, name          # isolated argmax near-ties may move single values
+    idx = model.buffer("idx1", torch.uint8, (1, H // 2, W // 2, 128)).permute(0, 3, 1, 2).cpu().long()
+    i1 = st["i1"]
+    exp_idx = ((i1 // W) % 2) * 2 + (i1 % W) % 2
+    assert (idx != exp_idx).float().mean().item() < 0.002
+
+
+@pytest.mark.parametrize("precision", _available_precisions())
+@pytest.mark.parametrize("cfgname,scans", [("kitti", ["hdl64_s0", "uniform_s0", "real_000000"]), ("camera", ["small_camera"])])
+def test_fused_infer_end_to_end(cfgname, scans, precision, cuda):
+    """Raw scans -> infer() -> height + labels, against the oracle's full reference call sequence
+    (predict_ground.py:110-121, :165-168)."""
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, scans, {}, precision, cuda)
+    nmax = max(len(r) for r in raws)
+    F = cfg.input_features
+    batch = np.full((len(raws), nmax, F), 1e9, dtype=np.float32)
+    for b, r in enumerate(raws):
+        batch[b, :len(r)] = r
+    counts = torch.tensor([len(r) for r in raws], dtype=torch.int32).cuda()
+    with torch.no_grad():
+        height, lab = model.infer(torch.from_numpy(batch).cuda(), threshold=0.08, counts=counts, labels="float64")
+    torch.cuda.synchronize()
+    # pillar bookkeeping equals the oracle's
+    pil = {k: t.cpu().numpy() for k, t in model.pillars(len(raws)).items()}
+    ofs = 0
+    for b in range(len(raws)):
+        m = int(pil["voxel_count"][b])
+        cb = c[c[:, 0] == b][:, 1:].astype(np.int32)
+        assert m == len(cb) and np.array_equal(pil["coors"][b, :m], cb)
+        assert np.array_equal(pil["num_points"][b, :m], n[ofs:ofs + m].astype(np.int32))
+        ofs += m
+    stable_max, frac_masked, overall = helpers.compare_heights(height, ref, st, TOL[precision])
+    print("infer %s %s: max|dh| stable=%.3g overall=%.3g masked=%.3f%%" % (cfgname, precision, stable_max, overall, 100 * frac_masked))
+    assert stable_max <= TOL[precision] and frac_masked < 0.05
+    refn = ref.numpy().reshape(len(raws), model.ny, model.nx)
+    total = same = 0
+    for b, p in enumerate(shifted):
+        exp = cpu_ops.segment_cloud(p.copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0], refn[b].T, 0.08)
+        got = lab[b, :len(p)].cpu().numpy()
+        assert got.dtype == np.float64 and set(np.unique(got)) <= {-1.0, 0.0, 1.0}
+        assert np.array_equal(got == -1, exp == -1), "range classification must be exact"
+        total += len(p)
+        same += int((got == exp).sum())
+        assert (lab[b, len(p):] == -1).all()
+    print("labels equal on %.4f%% of %d points" % (100.0 * same / total, total))
+    assert same / total >= 0.999
+
+
+def test_state_dict_keys_match_reference_layout(cuda):
+    from gndnet_b200.model import GroundEstimatorNet
+    for cfgname, ov in (("kitti", {}), ("camera", {}), ("kitti", dict(use_norm=True))):
+        cfg = synth.make_cfg(cfgname, **ov)
+        sd = synth.make_state_dict(cfg, 0, None)
+        m = GroundEstimatorNet(cfg)
+        own = m.state_dict()
+        assert set(own) == set(sd), set(own) ^ set(sd)
+        for k in sd:
+            assert tuple(own[k].shape) == tuple(np.asarray(sd[k]).shape), k
+
+
+def test_model_requires_cuda_and_loud_errors(cuda):
+    from gndnet_b200.model import GroundEstimatorNet
+    from gndnet_b200._lib import GndError
+    cfg = synth.make_cfg("kitti")
+    m = GroundEstimatorNet(cfg)
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 100, 4), torch.zeros(1, 4), torch.ones(1))
+    m = m.cuda().eval()
+    with pytest.raises((ValueError, GndError)):
+        m(torch.zeros(2, 100, 3).cuda(), torch.zeros(2, 4).cuda(), torch.ones(2).cuda())

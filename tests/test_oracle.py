@@ -1,0 +1,64 @@
+"""CPU: the oracle (C restatement + torch-fp32 model restatement) against the golden fixtures that
+oracle/ref_harness.py wrote while running the unmodified reference next to it."""
+import numpy as np
+import pytest
+
+from oracle import cpu_ops, model_ref, synth
+from tests import cases
+
+
+@pytest.mark.parametrize("name", [n for n in cases.CASES if n != "camera_1m"])
+def test_voxelizer_and_segment_match_reference_goldens(name):
+    cfg, raw, gold = cases.load_case(name)
+    assert synth.digest(cases.CASES[name][1]()) == gold["input_digest"], "synthetic input is not reproducible"
+    pts = raw.copy()
+    cpu_ops.shift_cloud(pts, cfg.lidar_height)
+    v, c, n, slot = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True,
+                                            cfg.max_voxels, return_point_slot=True)
+    assert len(n) == gold["M"]
+    assert synth.digest(v) == gold["voxels_digest"]
+    assert synth.digest(c) == gold["coors_digest"]
+    assert synth.digest(n) == gold["num_points_digest"]
+    assert synth.digest(slot) == gold["slot_digest"]
+    pred = cases.seg_test_map(cfg)
+    for thr, rec in gold["segment"].items():
+        if thr.startswith("noground"):
+            a, b = pts[:, :3].copy(), pts[:, :3].copy()
+            lab, obs = cpu_ops.segment_cloud_noground(a, b, np.asarray(cfg.grid_range), cfg.voxel_size[0], pred.T, 0.16)
+            assert len(obs) == rec["n_obs"] and synth.digest(obs) == rec["digest"]
+        else:
+            lab = cpu_ops.segment_cloud(pts.copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0], pred.T, float(thr))
+            assert synth.digest(lab.astype(np.int8)) == rec["digest"]
+            assert [int((lab == k).sum()) for k in (-1, 0, 1)] == rec["counts"]
+
+
+def test_small_case_arrays():
+    with np.load(cases.GOLDEN + "/small_cases.npz") as z:
+        for name in ("boundary_kitti", "small_kitti", "one_point", "boundary_camera", "small_camera"):
+            cfg, raw, _ = cases.load_case(name)
+            assert raw.tobytes() == z[name + ".points"][:, :cfg.input_features].tobytes()
+            pts = raw.copy()
+            cpu_ops.shift_cloud(pts, cfg.lidar_height)
+            _, c, n, slot = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True,
+                                                    cfg.max_voxels, return_point_slot=True)
+            assert np.array_equal(c, z[name + ".coors"]) and np.array_equal(n, z[name + ".num_points"])
+            assert np.array_equal(slot, z[name + ".slot"])
+
+
+def test_model_restatement_matches_reference_heights():
+    """camera + use_norm cases (small); the big kitti cases run in the GPU suite's oracle leg."""
+    with np.load(cases.GOLDEN + "/model_heights.npz") as z:
+        for key, scans, cfgname, ov in (("camera__small_camera", ["small_camera"], "camera", {}),
+                                        ("kitti__small_kitti_norm", ["small_kitti"], "kitti", dict(use_norm=True))):
+            cfg = synth.make_cfg(cfgname, batch_size=len(scans), **ov)
+            sd = synth.make_state_dict(cfg, 0, synth.load_bn_stats(cfgname))
+            vs, cs, ns = [], [], []
+            for b, s in enumerate(scans):
+                _, raw, _ = cases.load_case(s)
+                p = raw.copy()
+                cpu_ops.shift_cloud(p, cfg.lidar_height)
+                v, c, n = cpu_ops.points_to_voxel(p, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+                vs.append(v); ns.append(n.astype(np.float32))
+                cs.append(np.concatenate([np.full((len(c), 1), b, np.float32), c.astype(np.float32)], 1))
+            out = model_ref.forward(sd, cfg, np.concatenate(vs), np.concatenate(cs), np.concatenate(ns)).numpy()
+            assert np.abs(out - z[key]).max() <= 2e-5

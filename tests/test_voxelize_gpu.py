@@ -1,0 +1,112 @@
+"""GPU parity: the CUDA voxelizer against the CPU oracle (bit-exact) and the reference's golden digests."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_ops, synth
+from tests import cases
+
+pytestmark = pytest.mark.gpu
+
+
+def _shifted(cfg, raw):
+    p = raw.copy()
+    cpu_ops.shift_cloud(p, cfg.lidar_height)
+    return p
+
+
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_points_to_voxel_dropin_bit_exact(name, cuda):
+    """numpy in / numpy out, same call as predict_ground.py:114."""
+    from gndnet_b200.point_cloud_ops import points_to_voxel
+    cfg, raw, gold = cases.load_case(name)
+    pts = _shifted(cfg, raw)
+    keep = pts.copy()
+    v, c, n = points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+    assert pts.tobytes() == keep.tobytes(), "points_to_voxel must not mutate its input"
+    assert v.dtype == np.float32 and c.dtype == np.int32 and n.dtype == np.int32
+    ov, oc, on = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+    assert v.shape == ov.shape and len(n) == gold["M"]
+    assert c.tobytes() == oc.tobytes(), "coors differ"
+    assert n.tobytes() == on.tobytes(), "num_points differ"
+    assert v.tobytes() == ov.tobytes(), "voxels differ"
+    assert synth.digest(v) == gold["voxels_digest"] and synth.digest(c) == gold["coors_digest"]
+    assert synth.digest(n) == gold["num_points_digest"]
+
+
+@pytest.mark.parametrize("name", ["small_kitti", "boundary_kitti"])
+def test_points_to_voxel_non_reversed(name, cuda):
+    from gndnet_b200.point_cloud_ops import points_to_voxel
+    cfg, raw, _ = cases.load_case(name)
+    pts = _shifted(cfg, raw)
+    a = points_to_voxel(torch.from_numpy(pts).cuda(), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, False, cfg.max_voxels)
+    b = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, False, cfg.max_voxels)
+    assert all(x.is_cuda for x in a)
+    assert all(x.cpu().numpy().tobytes() == y.tobytes() for x, y in zip(a, b))
+
+
+def test_fused_batched_ragged_with_z_shift(cuda):
+    """The fused path: raw scans, z-shift inside the kernel, ragged batch via counts, pillar lists instead
+    of the dense tensor.  Every scan must equal the oracle run on that scan alone."""
+    from gndnet_b200.point_cloud_ops import voxelize_batch
+    names = ["hdl64_s0", "uniform_s0", "small_kitti", "empty", "boundary_kitti", "real_000000", "single_cell"]
+    loaded = [cases.load_case(n) for n in names]
+    cfg = loaded[0][0]
+    nmax = max(len(r) for _, r, _ in loaded)
+    batch = np.full((len(names), nmax, 4), 1e9, dtype=np.float32)          # padding rows are out of range anyway
+    counts = np.array([len(r) for _, r, _ in loaded], dtype=np.int32)
+    for b, (_, r, _) in enumerate(loaded):
+        batch[b, :len(r)] = r
+    out = voxelize_batch(torch.from_numpy(batch).cuda(), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel,
+                         cfg.max_voxels, True, counts=torch.from_numpy(counts).cuda(), z_shift=cfg.lidar_height,
+                         want_slot=True)
+    out = {k: v.cpu().numpy() for k, v in out.items()}
+    for b, (name, (_, raw, gold)) in enumerate(zip(names, loaded)):
+        pts = _shifted(cfg, raw)
+        _, oc, on, oslot = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True,
+                                                   cfg.max_voxels, return_point_slot=True)
+        m = int(out["voxel_count"][b])
+        assert m == len(on) == gold["M"], name
+        assert np.array_equal(out["coors"][b, :m], oc), name
+        assert np.array_equal(out["num_points"][b, :m], on), name
+        assert np.array_equal(out["point_slot"][b, :len(raw)].astype(np.int64), oslot), name
+        assert (out["point_slot"][b, len(raw):] == -1).all()
+        off = out["point_offsets"][b, :m + 1]
+        assert off[0] == 0 and np.array_equal(np.diff(off), on), name
+        # pillar lists: point indices of each voxel in input order
+        order = np.argsort(oslot[oslot >= 0], kind="stable")
+        expect = np.nonzero(oslot >= 0)[0][order]
+        assert np.array_equal(out["point_list"][b, :off[m]], expect.astype(np.int32)), name
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_random_grids_and_limits(seed, cuda):
+    """Random clouds over random grids / max_points / max_voxels, duplicates and shuffles included."""
+    from gndnet_b200.point_cloud_ops import points_to_voxel
+    rng = np.random.default_rng(100 + seed)
+    for _ in range(6):
+        n = int(rng.integers(1, 40000))
+        f = int(rng.choice([3, 4, 5]))
+        vs = [float(rng.choice([0.25, 0.4, 1.0, 2.5])), float(rng.choice([0.3, 0.5, 1.0])), float(rng.choice([2.0, 4.0, 8.0]))]
+        lo = [-float(rng.integers(5, 40)), -float(rng.integers(5, 40)), -4.0]
+        hi = [lo[0] + vs[0] * int(rng.integers(3, 150)), lo[1] + vs[1] * int(rng.integers(3, 150)), 4.0]
+        pts = (rng.random((n, f)) * 2 - 1).astype(np.float32) * np.array([60, 60, 5] + [1] * (f - 3), np.float32)
+        pts[rng.integers(0, n, n // 10)] = pts[rng.integers(0, n, n // 10)]       # duplicates
+        mp, mv = int(rng.choice([1, 3, 35, 100])), int(rng.choice([7, 100, 2000, 20000]))
+        got = points_to_voxel(pts, vs, lo + hi, mp, True, mv)
+        exp = cpu_ops.points_to_voxel(pts, vs, lo + hi, mp, True, mv)
+        for g, e in zip(got, exp):
+            assert g.shape == e.shape and g.tobytes() == e.tobytes()
+
+
+def test_nan_points_are_dropped(cuda):
+    from gndnet_b200.point_cloud_ops import points_to_voxel
+    cfg, raw, _ = cases.load_case("small_kitti")
+    pts = _shifted(cfg, raw)
+    bad = pts.copy()
+    bad[5, 0] = np.nan
+    bad[17, 2] = np.nan
+    got = points_to_voxel(bad, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+    exp = cpu_ops.points_to_voxel(np.delete(pts, [5, 17], axis=0), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+    for g, e in zip(got, exp):
+        assert g.tobytes() == e.tobytes()
