@@ -68,6 +68,7 @@ _SIGS = {
     "gnd_pfn_scatter": (ctypes.c_int, [c_vp, c_vp, c_i32, c_i64, c_vp]),
     "gnd_pfn_scatter_dense": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp]),
     "gnd_segnet": (ctypes.c_int, [c_vp, c_i32, c_vp, c_vp]),
+    "gnd_segnet_profile": (ctypes.c_int, [c_vp, c_i32, c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_f), c_vp]),
     "gnd_segment": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_vp, c_d, c_vp, c_vp, c_vp]),
     "gnd_infer": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_d, c_vp, c_vp, c_vp, c_vp]),
     "gnd_get_buffer": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),

@@ -183,6 +183,29 @@ extern "C" int gnd_segnet(gnd_ctx *ctx, int32_t batch, float *height, void *stre
     return rc;
 }
 
+// Profiling aid for bench.py's roofline: one gnd_segnet with CUDA events around each of the 8 convolution
+// launches.  SYNCHRONOUS.  h_conv_ms[8] = per-layer device time, *h_total_ms = the whole segnet.
+extern "C" int gnd_segnet_profile(gnd_ctx *ctx, int32_t batch, float *height, float *h_conv_ms, float *h_total_ms, void *stream) {
+    g_launches = 0;
+    int rc = check_bound(ctx, batch, -1, true);
+    if (rc != GND_OK) return rc;
+    if (!height || !h_conv_ms || !h_total_ms) return fail(GND_ERR_INVALID, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t ev[18];
+    for (int i = 0; i < 18; ++i) GND_CUDA_CHECK(cudaEventCreate(&ev[i]));
+    GND_CUDA_CHECK(cudaEventRecord(ev[16], st));
+    rc = segnet_run(ctx, batch, height, st, ev);
+    if (rc == GND_OK) {
+        GND_CUDA_CHECK(cudaEventRecord(ev[17], st));
+        GND_CUDA_CHECK(cudaStreamSynchronize(st));
+        for (int l = 0; l < 8; ++l) GND_CUDA_CHECK(cudaEventElapsedTime(&h_conv_ms[l], ev[2 * l], ev[2 * l + 1]));
+        GND_CUDA_CHECK(cudaEventElapsedTime(h_total_ms, ev[16], ev[17]));
+    }
+    for (int i = 0; i < 18; ++i) cudaEventDestroy(ev[i]);
+    ctx->last_launches = g_launches;
+    return rc;
+}
+
 static int segment_with_ctx(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch, int64_t n_points,
                             const float *height, double threshold, int8_t *labels_i8, double *labels_f64, cudaStream_t st) {
     gnd_segment_params sp;

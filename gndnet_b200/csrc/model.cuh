@@ -76,7 +76,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
 int pfn_scatter_dense_run(gnd_ctx *ctx, const float *voxels, const float *coors4, const float *num_points,
                           int64_t n_pillars, int32_t batch, cudaStream_t st);
 // segnet.cu
-int segnet_run(gnd_ctx *ctx, int32_t batch, float *height, cudaStream_t st);
+int segnet_run(gnd_ctx *ctx, int32_t batch, float *height, cudaStream_t st, cudaEvent_t *conv_events = nullptr);
 // conv_tc.cu (tcgen05 path)
 int tc_build_tensor_maps(gnd_ctx *ctx);
 void tc_free_tensor_maps(gnd_ctx *ctx);

@@ -233,13 +233,15 @@ static int conv_f32(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int 
     return GND_OK;
 }
 
-int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st) {
+int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEvent_t *ev) {
     const bool tc = ctx->cfg.precision != GND_PREC_FP32;
     int rc;
 #define CONV(l, in, out, fuse)                                                          \
     do {                                                                                \
+        if (ev) cudaEventRecord(ev[2 * (l)], st);                                        \
         rc = tc ? tc_conv_run(ctx, l, in, out, B, fuse, st) : conv_f32(ctx, l, in, out, B, st); \
         if (rc != GND_OK) return rc;                                                    \
+        if (ev) cudaEventRecord(ev[2 * (l) + 1], st);                                    \
     } while (0)
     CONV(0, ctx->canvas, ctx->d1a, false);
     CONV(1, ctx->d1a, ctx->d1b, false);

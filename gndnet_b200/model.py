@@ -305,6 +305,45 @@ class GroundEstimatorNet(nn.Module):
             return height[0], (lab[0] if lab is not None else None)
         return height, lab
 
+    def stage_times(self, points, height, labels, threshold=0.08, reps=3):
+        """Device milliseconds of each stage of one infer() over `points` (CUDA events around the stage entry
+        points of the C ABI; the convolution launches are timed individually by gnd_segnet_profile)."""
+        L = _lib.lib()
+        ctx = self._ensure_ctx()
+        B, N, _ = points.shape
+        self._ensure_workspace(B, N)
+        st = _lib.stream_ptr()
+        l8 = labels if labels.dtype == torch.int8 else None
+        l64 = labels if labels.dtype == torch.float64 else None
+        acc = dict(voxelize=0.0, pfn_scatter=0.0, segnet=0.0, segnet_convs=0.0, segment=0.0)
+        conv = np.zeros(8)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        for _ in range(reps):
+            ev[0].record()
+            _lib.check(L.gnd_voxelize(ctx, _lib.ptr(points), None, B, N, st), "gnd_voxelize")
+            ev[1].record()
+            _lib.check(L.gnd_pfn_scatter(ctx, _lib.ptr(points), B, N, st), "gnd_pfn_scatter")
+            ev[2].record()
+            cms = (ctypes.c_float * 8)()
+            tot = ctypes.c_float()
+            _lib.check(L.gnd_segnet_profile(ctx, B, _lib.ptr(height), cms, ctypes.byref(tot), st), "gnd_segnet_profile")
+            ev[3].record()
+            _lib.check(L.gnd_segment(ctx, _lib.ptr(points), None, B, N, _lib.ptr(height), float(threshold),
+                                     _lib.ptr(l8), _lib.ptr(l64), st), "gnd_segment")
+            end = torch.cuda.Event(enable_timing=True)
+            end.record()
+            torch.cuda.synchronize()
+            acc["voxelize"] += ev[0].elapsed_time(ev[1])
+            acc["pfn_scatter"] += ev[1].elapsed_time(ev[2])
+            acc["segnet"] += tot.value
+            acc["segnet_convs"] += float(sum(cms))
+            acc["segment"] += ev[3].elapsed_time(end)
+            conv += np.array(list(cms))
+        out = {k: v / reps for k, v in acc.items()}
+        out["conv_layers_ms"] = [float(x) / reps for x in conv]
+        out["conv_kernel"] = "conv3x3_f32_kernel" if self.precision == "fp32" else "conv3x3_tc_kernel"
+        return out
+
     def pillars(self, batch):
         """Voxelizer outputs of the last infer() as tensors (views of the workspace)."""
         mv = int(getattr(self.cfg, "max_voxels", self.nx * self.ny * self.nz))

@@ -187,6 +187,10 @@ GND_API int gnd_pfn_scatter_dense(gnd_ctx *ctx, const float *voxels, const float
                                   const float *num_points, int64_t n_pillars, int32_t batch, void *stream);
 /* Stage 3: segnetGndEst.forward (segnet.py:133-142) canvas -> height [batch][ny][nx] float32. */
 GND_API int gnd_segnet(gnd_ctx *ctx, int32_t batch, float *height, void *stream);
+/* Profiling aid (bench.py roofline): gnd_segnet with CUDA events around each of the 8 convolution
+ * launches; SYNCHRONOUS; h_conv_ms[8] per-layer device milliseconds, *h_total_ms the whole stage. */
+GND_API int gnd_segnet_profile(gnd_ctx *ctx, int32_t batch, float *height, float *h_conv_ms, float *h_total_ms,
+                               void *stream);
 /* Stage 4: labels for the raw scans against `height` (z-shift fused; grid_range frame). */
 GND_API int gnd_segment(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
                         int64_t n_points, const float *height, double threshold, int8_t *labels_i8,

@@ -37,39 +37,69 @@ def _dilate(mask, r):
     return m.squeeze(1) > 0
 
 
-def unstable_mask(st, rel=1e-4, abs_=1e-5):
-    """Output pixels whose value depends on a max-pool argmax that is a near-tie in the oracle.
+def _windows(x):
+    """[B,C,H,W] -> [B,C,H/2,W/2,4] (2x2 windows in row-major order, floor mode)."""
+    B, C, H, W = x.shape
+    return x[:, :, :H // 2 * 2, :W // 2 * 2].reshape(B, C, H // 2, 2, W // 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, C, H // 2, W // 2, 4)
+
+
+def _act(model, name, B, h, w, ch):
+    """A stage buffer of the CUDA path as an NCHW float tensor on the CPU (either activation format)."""
+    if model.precision == "fp32":
+        t = model.buffer(name, torch.float32, (B, h, w, ch)).float()
+    else:
+        t = model.buffer(name + ".hi", torch.float16, (B, h, w, ch)).float()
+        try:
+            t = t + model.buffer(name + ".lo", torch.float16, (B, h, w, ch)).float()
+        except Exception:
+            pass
+    return t.permute(0, 3, 1, 2).cpu()
+
+
+def flip_mask(model, st, tie_rel=2e-3, tie_abs=1e-4):
+    """Output pixels in the receptive field of a max-pool window whose argmax differs from the oracle's.
 
     MaxPool2d keeps ONE position per window (segnet.py:54,60) and MaxUnpool2d puts the value back there
     (segnet.py:84,89): when the two largest values of a window agree to rounding error, any implementation
     with a different summation order (the reference's own CUDA path included) may pick the other one, and
-    the output changes by O(activation) in the receptive field of that window.  Such pixels are excluded
-    from the height comparison (and counted)."""
-    def near_tie(x):                           # x [B,C,H,W] -> [B,H/2,W/2] any channel near-tied
-        B, C, H, W = x.shape
-        w = x[:, :, :H // 2 * 2, :W // 2 * 2].reshape(B, C, H // 2, 2, W // 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, C, H // 2, W // 2, 4)
-        top = torch.topk(w, 2, dim=-1).values
-        gap = top[..., 0] - top[..., 1]
-        tie = (gap <= abs_ + rel * top[..., 0].abs()) & (top[..., 0] > 0)
-        # an exact tie (gap == 0) between different positions is deterministic (first max) -> only rounding-level ties count
-        tie &= gap > 0
-        return tie.any(dim=1)
-    t1 = near_tie(st["d1b"])                   # [B,H1,W1]
-    t2 = near_tie(st["d2b"])                   # [B,H2,W2]
-    B, H, W = st["out"].shape[0], st["out"].shape[2], st["out"].shape[3]
+    the output then changes by O(activation) around that window.  A differing argmax is accepted ONLY where
+    the oracle's window is such a near-tie (asserted here); those pixels are excluded from the height
+    comparison and counted."""
+    B, _, H, W = st["out"].shape
+    H1, W1 = st["d2b"].shape[2], st["d2b"].shape[3]
+
+    def near_tie(x):
+        top = torch.topk(_windows(x), 2, dim=-1).values
+        return (top[..., 0] - top[..., 1]) <= tie_abs + tie_rel * top[..., 0].abs()
+
+    # level 1: recorded argmax of down1's pool
+    idx = model.buffer("idx1", torch.uint8, (B, H // 2, W // 2, 128)).permute(0, 3, 1, 2).cpu().long()
+    i1 = st["i1"]
+    exp1 = ((i1 // W) % 2) * 2 + (i1 % W) % 2
+    f1 = idx != exp1
+    assert bool((near_tie(st["d1b"]) | ~f1).all()), "pool-1 argmax differs from the oracle where it is not a near-tie"
+    # level 2: which position of each window survived pool+unpool
+    u2 = _act(model, "u2", B, H1, W1, 256)
+    d2b = st["d2b"]
+    wmax = _windows(d2b).max(dim=-1).values
+    pos_or = _windows(st["u2"]) != 0
+    pos_us = _windows(u2) != 0
+    f2 = (pos_or != pos_us).any(dim=-1) & (wmax > 0)
+    assert bool((near_tie(d2b) | ~f2).all()), "pool-2 argmax differs from the oracle where it is not a near-tie"
+    t1, t2 = f1.any(dim=1), f2.any(dim=1)
     up = lambda m, h, w: torch.nn.functional.pad(m.repeat_interleave(2, 1).repeat_interleave(2, 2),
                                                  (0, w - 2 * m.shape[2], 0, h - 2 * m.shape[1]))
-    H1, W1 = st["d2b"].shape[2], st["d2b"].shape[3]
     m2 = _dilate(up(t2, H1, W1), 2)            # through up2.conv1, up2.conv2 at half resolution
     m = up(m2, H, W) | up(t1, H, W)
-    return _dilate(m, 3)                       # through up1.conv1, up1.conv2, regressor
+    return _dilate(m, 3), int(f1.sum()), int(f2.sum())      # through up1.conv1, up1.conv2, regressor
 
 
-def compare_heights(out, ref, st, tol):
-    """-> (max |d| on stable pixels, fraction masked, max |d| overall)."""
-    out = torch.as_tensor(out).reshape(st["out"].shape[0], st["out"].shape[2], st["out"].shape[3]).cpu()
+def compare_heights(model, out, ref, st):
+    """-> (max |d| on unaffected pixels, fraction of pixels masked, max |d| overall, (#flips level 1, level 2))."""
+    B, _, H, W = st["out"].shape
+    out = torch.as_tensor(out).reshape(B, H, W).cpu()
     ref = torch.as_tensor(ref).reshape(out.shape)
     d = (out - ref).abs()
-    mask = unstable_mask(st)
+    mask, n1, n2 = flip_mask(model, st)
     stable = d[~mask]
-    return float(stable.max()) if stable.numel() else 0.0, float(mask.float().mean()), float(d.max())
+    return float(stable.max()) if stable.numel() else 0.0, float(mask.float().mean()), float(d.max()), (n1, n2)
