@@ -101,6 +101,132 @@ __global__ void __launch_bounds__(256) unpool_kernel(const Act in, const uint8_t
     }
 }
 
+// ---- vectorised fp16 (hi [+ lo]) versions: 8 channels (one 16-byte vector per plane) per thread --------
+struct H8 { float v[8]; };
+
+__device__ __forceinline__ H8 load_h8(const Act &a, size_t i) {
+    H8 r;
+    const uint4 h = __ldg(reinterpret_cast<const uint4 *>(a.hi + i));
+    const __half2 *hp = reinterpret_cast<const __half2 *>(&h);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { float2 f = __half22float2(hp[k]); r.v[2 * k] = f.x; r.v[2 * k + 1] = f.y; }
+    if (a.lo) {
+        const uint4 l = __ldg(reinterpret_cast<const uint4 *>(a.lo + i));
+        const __half2 *lp = reinterpret_cast<const __half2 *>(&l);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { float2 f = __half22float2(lp[k]); r.v[2 * k] += f.x; r.v[2 * k + 1] += f.y; }
+    }
+    return r;
+}
+
+__device__ __forceinline__ void store_h8(const Act &a, size_t i, const H8 &x) {
+    uint4 h, l;
+    __half2 *hp = reinterpret_cast<__half2 *>(&h), *lp = reinterpret_cast<__half2 *>(&l);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        hp[k] = __floats2half2_rn(x.v[2 * k], x.v[2 * k + 1]);
+        const float2 b = __half22float2(hp[k]);
+        lp[k] = __floats2half2_rn(x.v[2 * k] - b.x, x.v[2 * k + 1] - b.y);
+    }
+    *reinterpret_cast<uint4 *>(a.hi + i) = h;
+    if (a.lo) *reinterpret_cast<uint4 *>(a.lo + i) = l;
+}
+
+// one thread per (pooled pixel, 8 channels)
+__global__ void __launch_bounds__(256) pool_h8_kernel(const Act in, const Act out, uint8_t *idx, int B) {
+    const int C8 = in.C / 8, Ho = out.H, Wo = out.W;
+    const size_t total = (size_t)B * Ho * Wo * C8;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C8) * 8;
+        size_t p = g / C8;
+        const int wo = (int)(p % Wo); p /= Wo;
+        const int ho = (int)(p % Ho);
+        const int b = (int)(p / Ho);
+        const size_t r0 = (((size_t)b * in.H + 2 * ho) * in.W + 2 * wo) * in.C + c;
+        const size_t r1 = r0 + (size_t)in.W * in.C;
+        const H8 a = load_h8(in, r0), bb = load_h8(in, r0 + in.C), cc = load_h8(in, r1), d = load_h8(in, r1 + in.C);
+        H8 m;
+        uint32_t klo = 0, khi = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int w = window_argmax(a.v[k], bb.v[k], cc.v[k], d.v[k], &m.v[k]);
+            if (k < 4) klo |= (uint32_t)w << (8 * k); else khi |= (uint32_t)w << (8 * (k - 4));
+        }
+        const size_t o = g * 8;
+        store_h8(out, o, m);
+        *reinterpret_cast<uint2 *>(idx + o) = make_uint2(klo, khi);
+    }
+}
+
+// one thread per (2x2 window incl. partial border windows, 8 channels)
+__global__ void __launch_bounds__(256) pool_mask_h8_kernel(const Act in, const Act out, int B) {
+    const int C8 = in.C / 8, H = in.H, W = in.W, Hp = H / 2, Wp = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2;
+    const size_t total = (size_t)B * Hc * Wc * C8;
+    H8 zero;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) zero.v[k] = 0.0f;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C8) * 8;
+        size_t p = g / C8;
+        const int wc = (int)(p % Wc); p /= Wc;
+        const int hc = (int)(p % Hc);
+        const int b = (int)(p / Hc);
+        const size_t r0 = (((size_t)b * H + 2 * hc) * W + 2 * wc) * in.C + c;
+        const size_t r1 = r0 + (size_t)W * in.C;
+        if (hc < Hp && wc < Wp) {
+            const H8 a = load_h8(in, r0), bb = load_h8(in, r0 + in.C), cc = load_h8(in, r1), d = load_h8(in, r1 + in.C);
+            H8 o0 = zero, o1 = zero, o2 = zero, o3 = zero;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float m;
+                const int w = window_argmax(a.v[k], bb.v[k], cc.v[k], d.v[k], &m);
+                if (w == 0) o0.v[k] = m; else if (w == 1) o1.v[k] = m; else if (w == 2) o2.v[k] = m; else o3.v[k] = m;
+            }
+            store_h8(out, r0, o0); store_h8(out, r0 + in.C, o1); store_h8(out, r1, o2); store_h8(out, r1 + in.C, o3);
+        } else {                                   // floor mode: the odd last row / column is never pooled -> zeros
+            const bool h1 = 2 * hc + 1 < H, w1 = 2 * wc + 1 < W;
+            store_h8(out, r0, zero);
+            if (w1) store_h8(out, r0 + in.C, zero);
+            if (h1) store_h8(out, r1, zero);
+            if (h1 && w1) store_h8(out, r1 + in.C, zero);
+        }
+    }
+}
+
+// one thread per (2x2 output window incl. partial border windows, 8 channels)
+__global__ void __launch_bounds__(256) unpool_h8_kernel(const Act in, const uint8_t *idx, const Act out, int B) {
+    const int C8 = out.C / 8, H = out.H, W = out.W, Hp = in.H, Wp = in.W, Hc = (H + 1) / 2, Wc = (W + 1) / 2;
+    const size_t total = (size_t)B * Hc * Wc * C8;
+    H8 zero;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) zero.v[k] = 0.0f;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+        const int c = (int)(g % C8) * 8;
+        size_t p = g / C8;
+        const int wc = (int)(p % Wc); p /= Wc;
+        const int hc = (int)(p % Hc);
+        const int b = (int)(p / Hc);
+        const size_t r0 = (((size_t)b * H + 2 * hc) * W + 2 * wc) * out.C + c;
+        const size_t r1 = r0 + (size_t)W * out.C;
+        const bool h1 = 2 * hc + 1 < H, w1 = 2 * wc + 1 < W;
+        H8 o0 = zero, o1 = zero, o2 = zero, o3 = zero;
+        if (hc < Hp && wc < Wp) {
+            const size_t s = (((size_t)b * Hp + hc) * Wp + wc) * out.C + c;
+            const H8 v = load_h8(in, s);
+            const uint2 kk = __ldg(reinterpret_cast<const uint2 *>(idx + s));
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int w = (int)(((k < 4 ? kk.x : kk.y) >> (8 * (k & 3))) & 0xff);
+                if (w == 0) o0.v[k] = v.v[k]; else if (w == 1) o1.v[k] = v.v[k]; else if (w == 2) o2.v[k] = v.v[k]; else o3.v[k] = v.v[k];
+            }
+        }
+        store_h8(out, r0, o0);
+        if (w1) store_h8(out, r0 + out.C, o1);
+        if (h1) store_h8(out, r1, o2);
+        if (h1 && w1) store_h8(out, r1 + out.C, o3);
+    }
+}
+
 // ---- strict fp32 convolution: 8x8 pixels x 64 output channels per CTA, 4x4 outputs per thread ----
 __global__ void __launch_bounds__(256) conv3x3_f32_kernel(const float *__restrict__ in, const float *__restrict__ w,
                                                           const float *__restrict__ bias, float *__restrict__ out,
@@ -245,15 +371,18 @@ int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEven
     } while (0)
     CONV(0, ctx->canvas, ctx->d1a, false);
     CONV(1, ctx->d1a, ctx->d1b, false);
-    pool_kernel<<<ew_blocks(ctx->p1.elems(B)), 256, 0, st>>>(ctx->d1b, ctx->p1, ctx->idx1, B);
+    if (tc) pool_h8_kernel<<<ew_blocks(ctx->p1.elems(B) / 8), 256, 0, st>>>(ctx->d1b, ctx->p1, ctx->idx1, B);
+    else pool_kernel<<<ew_blocks(ctx->p1.elems(B)), 256, 0, st>>>(ctx->d1b, ctx->p1, ctx->idx1, B);
     GND_LAUNCH_CHECK("pool_kernel");
     CONV(2, ctx->p1, ctx->d2a, false);
     CONV(3, ctx->d2a, ctx->d2b, false);
-    pool_mask_kernel<<<ew_blocks(ctx->u2.elems(B)), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
+    if (tc) pool_mask_h8_kernel<<<ew_blocks(ctx->u2.elems(B) / 32 + 1), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
+    else pool_mask_kernel<<<ew_blocks(ctx->u2.elems(B)), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
     GND_LAUNCH_CHECK("pool_mask_kernel");
     CONV(4, ctx->u2, ctx->u2a, false);
     CONV(5, ctx->u2a, ctx->u2b, false);
-    unpool_kernel<<<ew_blocks(ctx->u1.elems(B)), 256, 0, st>>>(ctx->u2b, ctx->idx1, ctx->u1, B);
+    if (tc) unpool_h8_kernel<<<ew_blocks(ctx->u1.elems(B) / 32 + 1), 256, 0, st>>>(ctx->u2b, ctx->idx1, ctx->u1, B);
+    else unpool_kernel<<<ew_blocks(ctx->u1.elems(B)), 256, 0, st>>>(ctx->u2b, ctx->idx1, ctx->u1, B);
     GND_LAUNCH_CHECK("unpool_kernel");
     CONV(6, ctx->u1, ctx->u1a, false);
     CONV(7, ctx->u1a, ctx->u1b, tc);

@@ -98,7 +98,7 @@ class GroundEstimatorNet(nn.Module):
     def __init__(self, cfg, precision=None):
         super().__init__()
         self.cfg = cfg
-        self.precision = precision or getattr(cfg, "precision", "fp32")
+        self.precision = precision or getattr(cfg, "precision", "mixed")
         if self.precision not in _lib.PRECISIONS:
             raise ValueError("precision must be one of %s" % sorted(_lib.PRECISIONS))
         self.voxel_feature_extractor = PillarFeatureNet(

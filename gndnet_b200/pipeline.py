@@ -1,0 +1,72 @@
+"""Streaming front end for host-resident scans: pinned H2D copy, the fused device path and the D2H read of
+the results run on three CUDA streams, so consecutive batches overlap (copy-in of batch i+1 and copy-out
+of batch i-1 under the compute of batch i).  This is the deployment shape of ros_node.py's loop
+(:96-126: take the latest cloud -> voxelize -> H2D -> model -> D2H of the map), batched.
+
+No collective and no cross-GPU traffic: one ScanStream per GPU, scans sharded by the caller.
+"""
+import torch
+
+
+class ScanStream:
+    def __init__(self, model, batch, n_points, depth=2, labels="int8", threshold=0.08):
+        self.model, self.depth, self.threshold = model, depth, threshold
+        dev = model._device()
+        self.dev = dev
+        F = model.cfg.input_features
+        ldt = {"int8": torch.int8, "float64": torch.float64}[labels]
+        with torch.cuda.device(dev):
+            self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+            self.slots = []
+            for _ in range(depth):
+                self.slots.append(dict(
+                    points=torch.empty((batch, n_points, F), dtype=torch.float32, device=dev),
+                    height=torch.empty((batch, model.ny, model.nx), dtype=torch.float32, device=dev),
+                    labels=torch.empty((batch, n_points), dtype=ldt, device=dev),
+                    h_height=torch.empty((batch, model.ny, model.nx), dtype=torch.float32).pin_memory(),
+                    h_labels=torch.empty((batch, n_points), dtype=ldt).pin_memory(),
+                    ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event(), used=False))
+        self.n = 0
+        self.h2d_bytes = batch * n_points * F * 4
+        self.d2h_bytes = batch * (model.ny * model.nx * 4 + n_points * (1 if ldt == torch.int8 else 8))
+
+    def submit(self, host_points):
+        """Enqueue one batch of pinned host scans [B, N, F]; returns the slot holding its results."""
+        k = self.n % self.depth
+        s = self.slots[k]
+        cur = torch.cuda.current_stream(self.dev)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.s_in.wait_event(ev)                       # ordered after the caller's earlier work
+        if s["used"]:
+            self.s_in.wait_event(s["ev_done"])         # the slot's previous scans have been consumed
+        with torch.cuda.stream(self.s_in):
+            s["points"].copy_(host_points, non_blocking=True)
+            s["ev_in"].record()
+        self.s_cmp.wait_event(s["ev_in"])
+        if s["used"]:
+            self.s_cmp.wait_event(s["ev_out"])         # the slot's previous results have been read out
+        with torch.cuda.stream(self.s_cmp):
+            self.model.infer(s["points"], threshold=self.threshold, out=(s["height"], s["labels"]))
+            s["ev_done"].record()
+        self.s_out.wait_event(s["ev_done"])
+        with torch.cuda.stream(self.s_out):
+            s["h_height"].copy_(s["height"], non_blocking=True)
+            s["h_labels"].copy_(s["labels"], non_blocking=True)
+            s["ev_out"].record()
+        s["used"] = True
+        self.n += 1
+        return k
+
+    def drain(self):
+        """Make the caller's current stream wait for everything submitted so far."""
+        cur = torch.cuda.current_stream(self.dev)
+        for s in self.slots:
+            if s["used"]:
+                cur.wait_event(s["ev_out"])
+
+    def result(self, slot):
+        """Host tensors (height [B,ny,nx], labels [B,N]) of a submitted batch; blocks until they are there."""
+        s = self.slots[slot]
+        s["ev_out"].synchronize()
+        return s["h_height"], s["h_labels"]

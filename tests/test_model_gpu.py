@@ -16,7 +16,7 @@ TOL = {"fp32": 1e-3, "split": 1e-3, "mixed": 5e-3}
 
 
 def _available_precisions():
-    return ["fp32"]
+    return ["fp32", "mixed", "split"]
 
 
 def _run_case(cfgname, scans, overrides, precision, device):
@@ -54,7 +54,7 @@ def test_forward_dropin_matches_oracle_and_golden(cfgname, scans, overrides, key
     stable_max, frac_masked, overall, flips = helpers.compare_heights(model, out, ref, st)
     print("%s %s: max|dh| unaffected=%.3g overall=%.3g argmax flips=%s masked=%.3f%% canvas=%.3g" %
           (key, precision, stable_max, overall, flips, 100 * frac_masked, dc))
-    assert frac_masked < 0.05
+    assert flips[0] <= 1e-4 * st["p1"].numel() + 2 and flips[1] <= 1e-4 * st["p2"].numel() + 2, "too many argmax flips"
     assert stable_max <= TOL[precision]
     with np.load(cases.GOLDEN + "/model_heights.npz") as z:
         gold = torch.from_numpy(z[key])
@@ -63,25 +63,29 @@ def test_forward_dropin_matches_oracle_and_golden(cfgname, scans, overrides, key
 
 
 @pytest.mark.parametrize("precision", _available_precisions())
-def test_fp32_stage_by_stage(precision, cuda):
-    """Every intermediate activation of the fp32 path against the oracle's (pool / unpool semantics included)."""
-    if precision != "fp32":
-        pytest.skip("stage buffers are fp32 only in fp32 mode")
-    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case("camera", ["small_camera"], {}, precision, cuda)
+@pytest.mark.parametrize("cfgname,scan", [("camera", "small_camera"), ("kitti", "hdl64_s0")])
+def test_stage_by_stage(cfgname, scan, precision, cuda):
+    """Every intermediate activation against the oracle's (conv blocks, pool / unpool semantics)."""
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, [scan], {}, precision, cuda)
     with torch.no_grad():
         model(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
     H, W = model.ny, model.nx
     shapes = dict(d1a=(H, W, 128), d1b=(H, W, 128), p1=(H // 2, W // 2, 128), d2a=(H // 2, W // 2, 256),
                   d2b=(H // 2, W // 2, 256), u2=(H // 2, W // 2, 256), u2a=(H // 2, W // 2, 256),
                   u2b=(H // 2, W // 2, 128), u1=(H, W, 128), u1a=(H, W, 128), u1b=(H, W, 64))
+    if precision != "fp32":
+        del shapes["u1b"]            # never materialised: the regressor is fused into the last conv
+    # relative tolerance per stage: fp32-class where operands are fp32 / split-fp16, fp16-class in mixed's decoder
     for name, (h, w, ch) in shapes.items():
-        got = model.buffer(name, torch.float32, (1, h, w, ch)).permute(0, 3, 1, 2).cpu()
+        got = helpers._act(model, name, 1, h, w, ch)
         exp = st[name]
         d = (got - exp).abs()
         scale = max(1.0, exp.abs().max().item())
-        bad = (d > 1e-4 * scale).float().mean().item()
-        print("%-4s max|d|=%.3g  frac>1e-4=%.4f" % (name, d.max().item(), bad))
-        assert bad < 0.002, name          # isolated argmax near-ties may move single values
+        fp16_stage = precision == "mixed" and name in ("u2", "u2a", "u2b", "u1", "u1a")
+        tol = (4e-3 if fp16_stage else 1e-4) * scale
+        bad = (d > tol).float().mean().item()
+        print("%-4s %-5s max|d|=%.3g  frac>tol=%.5f (scale %.3g)" % (name, precision, d.max().item(), bad, scale))
+        assert bad < 0.003, name          # isolated argmax near-ties may move single values
     idx = model.buffer("idx1", torch.uint8, (1, H // 2, W // 2, 128)).permute(0, 3, 1, 2).cpu().long()
     i1 = st["i1"]
     exp_idx = ((i1 // W) % 2) * 2 + (i1 % W) % 2
@@ -115,7 +119,8 @@ def test_fused_infer_end_to_end(cfgname, scans, precision, cuda):
     stable_max, frac_masked, overall, flips = helpers.compare_heights(model, height, ref, st)
     print("infer %s %s: max|dh| unaffected=%.3g overall=%.3g argmax flips=%s masked=%.3f%%" %
           (cfgname, precision, stable_max, overall, flips, 100 * frac_masked))
-    assert stable_max <= TOL[precision] and frac_masked < 0.05
+    assert stable_max <= TOL[precision]
+    assert flips[0] <= 1e-4 * st["p1"].numel() + 2 and flips[1] <= 1e-4 * st["p2"].numel() + 2, "too many argmax flips"
     refn = ref.numpy().reshape(len(raws), model.ny, model.nx)
     total = same = 0
     for b, p in enumerate(shifted):
