@@ -33,6 +33,7 @@ struct ConvLayer {
 };
 
 struct TensorMaps;   // conv_tc.cu
+struct HaloMaps;     // conv_halo.cu
 
 }  // namespace gnd
 
@@ -65,6 +66,7 @@ struct gnd_ctx {
     uint8_t *idx1 = nullptr;   // [B][H1][W1][128] argmax (0..3) of down1's pool
     float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
     gnd::TensorMaps *tmaps = nullptr;
+    gnd::HaloMaps *hmaps = nullptr;
 
     int last_launches = 0;
 };
@@ -81,6 +83,11 @@ int segnet_run(gnd_ctx *ctx, int32_t batch, float *height, cudaStream_t st, cuda
 int tc_build_tensor_maps(gnd_ctx *ctx);
 void tc_free_tensor_maps(gnd_ctx *ctx);
 int tc_conv_run(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
+// conv_halo.cu (tcgen05 path, halo staged once per channel block)
+int halo_build(gnd_ctx *ctx, const Act *const inputs[8]);
+void halo_free(gnd_ctx *ctx);
+bool halo_usable(const gnd_ctx *ctx, int layer);
+int halo_conv_run(gnd_ctx *ctx, int layer, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
 // segment.cu
 int segment_run(const gnd_segment_params *p, float *points, const int32_t *counts, int32_t batch,
                 int64_t n_points, const float *elevation, double *labels_f64, int8_t *labels_i8,
