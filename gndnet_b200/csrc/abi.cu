@@ -20,7 +20,7 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
     Carver c(ws);
     const gnd_config &cfg = ctx->cfg;
     // voxelizer scratch + outputs
-    c.off += vox_carve(ctx->vplan, B, N, ws, ws ? &ctx->vws : nullptr);
+    c.off += vox_carve(ctx->vplan, B, N, ws, ws ? &ctx->vws : nullptr, true);
     const size_t mv = (size_t)cfg.max_voxels;
     int32_t *coors = c.take<int32_t>((size_t)B * mv * 3);
     int32_t *num = c.take<int32_t>((size_t)B * mv);

@@ -35,8 +35,9 @@ struct PfnArgs {
     float z_shift;
     const float *w;             // [nfeat][64]
     const float *bias;          // [64]
-    // fused inputs
-    const int32_t *vid, *num, *off, *list;
+    // fused inputs: kept points grouped by cell (voxelize.cu)
+    const int32_t *offc;
+    const float4 *sorted;
     // dense inputs
     const float *coors4, *num_f;
     int64_t M;
@@ -114,49 +115,99 @@ __device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s
     }
 }
 
+// Fused path: the voxelizer left the kept points grouped by CELL (`sorted`, CSR `offc`), z already shifted.
+// One warp walks 32 consecutive cells; lane l owns channels 2l, 2l+1.  The Linear is regrouped around the
+// pillar centre so that a point costs 4 multiply-adds per channel instead of 9:
+//   W f + b = A x' + B y' + C z + D r (+ Wd |p|) + E,   x' = x - cx,  y' = y - cy,
+//   A = w_x + w_dmx + w_dcx,  B = w_y + w_dmy + w_dcy,  C = w_z + w_dmz,  D = w_r,
+//   E = b + w_x cx + w_y cy + w_dmx (cx - mean_x) + w_dmy (cy - mean_y) - w_dmz mean_z     (per pillar)
+// and relu(max_p(t_p + E)) = relu(max_p t_p + E).  All products stay below |w| in magnitude except E, whose
+// rounding (|w| * 50 m * 2^-24) is the same as the reference's own w_x * x term.
 __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnArgs a) {
-    __shared__ float s_feat[PFN_WARPS][32][FEAT_STRIDE];
+    __shared__ float4 s_pt[PFN_WARPS][32];
+    __shared__ float s_dist[PFN_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float w0[PFN_MAX_FEAT], w1[PFN_MAX_FEAT];
-#pragma unroll
-    for (int k = 0; k < PFN_MAX_FEAT; ++k) {
-        w0[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane) : 0.0f;
-        w1[k] = (k < a.nfeat) ? __ldg(a.w + k * PFN_OUT + 2 * lane + 1) : 0.0f;
-    }
-    const float b0 = __ldg(a.bias + 2 * lane), b1 = __ldg(a.bias + 2 * lane + 1);
+    const int kf = a.F > 3 ? 4 : 3;
+    auto W = [&](int k, int ch) { return __ldg(a.w + k * PFN_OUT + ch); };
+    const int ch0 = 2 * lane, ch1 = 2 * lane + 1;
+    const float wx0 = W(0, ch0), wx1 = W(0, ch1), wy0 = W(1, ch0), wy1 = W(1, ch1);
+    const float wmx0 = W(kf, ch0), wmx1 = W(kf, ch1), wmy0 = W(kf + 1, ch0), wmy1 = W(kf + 1, ch1);
+    const float wmz0 = W(kf + 2, ch0), wmz1 = W(kf + 2, ch1);
+    const float A0 = wx0 + wmx0 + W(kf + 3, ch0), A1 = wx1 + wmx1 + W(kf + 3, ch1);
+    const float B0 = wy0 + wmy0 + W(kf + 4, ch0), B1 = wy1 + wmy1 + W(kf + 4, ch1);
+    const float C0 = W(2, ch0) + wmz0, C1 = W(2, ch1) + wmz1;
+    const float D0 = kf == 4 ? W(3, ch0) : 0.0f, D1 = kf == 4 ? W(3, ch1) : 0.0f;
+    const float G0 = a.with_distance ? W(kf + 5, ch0) : 0.0f, G1 = a.with_distance ? W(kf + 5, ch1) : 0.0f;
+    const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
     const int cells = a.nx * a.ny;
-    const int64_t total = (int64_t)a.B * cells;
-    const bool vec4 = (a.F == 4) && ((((uintptr_t)a.points) & 15) == 0);
+    const int groups = (cells + 31) / 32;
+    const int64_t total = (int64_t)a.B * groups;
     for (int64_t g = (int64_t)blockIdx.x * PFN_WARPS + warp; g < total; g += (int64_t)gridDim.x * PFN_WARPS) {
-        const int b = (int)(g / cells), c = (int)(g - (int64_t)b * cells);
-        const int v = __ldg(a.vid + g);
-        float m0 = 0.0f, m1 = 0.0f;
-        if (v >= 0) {
-            const int n = __ldg(a.num + (int64_t)b * a.max_voxels + v);
-            const int o = __ldg(a.off + (int64_t)b * (a.max_voxels + 1) + v);
-            const int32_t *lst = a.list + (int64_t)b * a.N + o;
-            const float *pts = a.points + (int64_t)b * a.N * a.F;
-            auto fetch = [&](int j, float &x, float &y, float &z, float &r) {
-                const int i = __ldg(lst + j);
-                load_point(pts + (int64_t)i * a.F, a.F, vec4, x, y, z, r);
-                if (a.apply_shift) z = __fadd_rn(z, a.z_shift);
-            };
-            float sx = 0.f, sy = 0.f, sz = 0.f;
-            for (int j = lane; j < n; j += 32) {
-                float x, y, z, r;
-                fetch(j, x, y, z, r);
-                sx += x; sy += y; sz += z;
-            }
+        const int b = (int)(g / groups), c0 = (int)(g - (int64_t)b * groups) * 32;
+        const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
+        const float4 *pts = a.sorted + (int64_t)b * a.N;
+        const int cl = min(c0 + lane, cells);
+        const int my_o = __ldg(offc + cl);
+        const int my_n = __ldg(offc + min(cl + 1, cells)) - my_o;
+        const int ncell = min(32, cells - c0);
+        for (int j = 0; j < ncell; ++j) {
+            const int n = __shfl_sync(0xffffffffu, my_n, j);
+            const int o = __shfl_sync(0xffffffffu, my_o, j);
+            const int c = c0 + j;
+            float m0 = 0.0f, m1 = 0.0f;
+            if (n > 0) {
+                // :120 points_mean = sum over the pillar's slots / num_points
+                float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (lane < n) p0 = __ldg(pts + o + lane);
+                float sx = p0.x, sy = p0.y, sz = p0.z;
+                for (int q = 32 + lane; q < n; q += 32) { const float4 p = __ldg(pts + o + q); sx += p.x; sy += p.y; sz += p.z; }
 #pragma unroll
-            for (int d = 16; d > 0; d >>= 1) {
-                sx += __shfl_xor_sync(0xffffffffu, sx, d);
-                sy += __shfl_xor_sync(0xffffffffu, sy, d);
-                sz += __shfl_xor_sync(0xffffffffu, sz, d);
+                for (int d = 16; d > 0; d >>= 1) {
+                    sx += __shfl_xor_sync(0xffffffffu, sx, d);
+                    sy += __shfl_xor_sync(0xffffffffu, sy, d);
+                    sz += __shfl_xor_sync(0xffffffffu, sz, d);
+                }
+                const float nf = (float)n;
+                const float mx = __fdiv_rn(sx, nf), my = __fdiv_rn(sy, nf), mz = __fdiv_rn(sz, nf);
+                // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
+                const float pcx = __fadd_rn(__fmul_rn((float)(c % a.nx), a.vx), a.xoff);
+                const float pcy = __fadd_rn(__fmul_rn((float)(c / a.nx), a.vy), a.yoff);
+                const float dmx = pcx - mx, dmy = pcy - my;
+                const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(wmx0, dmx, fmaf(wmy0, dmy, fmaf(-wmz0, mz, b0)))));
+                const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(wmx1, dmx, fmaf(wmy1, dmy, fmaf(-wmz1, mz, b1)))));
+                float t0 = -INFINITY, t1 = -INFINITY;
+                for (int q0 = 0; q0 < n; q0 += 32) {
+                    if (q0 + lane < n) {
+                        const float4 p = (q0 == 0) ? p0 : __ldg(pts + o + q0 + lane);
+                        s_pt[warp][lane] = make_float4(p.x - pcx, p.y - pcy, p.z, p.w);
+                        if (a.with_distance) s_dist[warp][lane] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p.x, p.x), __fmul_rn(p.y, p.y)), __fmul_rn(p.z, p.z)));
+                    }
+                    __syncwarp();
+                    const int cnt = min(32, n - q0);
+                    if (a.with_distance) {
+                        for (int q = 0; q < cnt; ++q) {
+                            const float4 f = s_pt[warp][q];
+                            const float dq = s_dist[warp][q];
+                            t0 = fmaxf(t0, fmaf(G0, dq, fmaf(D0, f.w, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x)))));
+                            t1 = fmaxf(t1, fmaf(G1, dq, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x)))));
+                        }
+                    } else {
+#pragma unroll 4
+                        for (int q = 0; q < cnt; ++q) {
+                            const float4 f = s_pt[warp][q];
+                            t0 = fmaxf(t0, fmaf(D0, f.w, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x))));
+                            t1 = fmaxf(t1, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x))));
+                        }
+                    }
+                    __syncwarp();
+                }
+                m0 = fmaxf(t0 + E0, 0.0f);
+                m1 = fmaxf(t1 + E1, 0.0f);
+                // padded slots give relu(b') (:137-140 then :54-58)
+                if (n < a.P) { m0 = fmaxf(m0, b0); m1 = fmaxf(m1, b1); }
             }
-            pfn_pillar(a, lane, s_feat[warp], w0, w1, b0, b1, n, sx, sy, sz, (float)n, (float)(c % a.nx),
-                       (float)(c / a.nx), fetch, m0, m1);
+            store_cell(a, (int64_t)b * cells + c, lane, m0, m1);
         }
-        store_cell(a, g, lane, m0, m1);
     }
 }
 
@@ -226,8 +277,9 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     fill_common(ctx, a, batch);
     a.points = points; a.N = n_points;
     a.apply_shift = 1; a.z_shift = ctx->cfg.lidar_height;
-    a.vid = ctx->vws.vid; a.num = ctx->num_points; a.off = ctx->offsets; a.list = ctx->list;
-    int64_t warps = (int64_t)batch * ctx->nx * ctx->ny;
+    if (!ctx->vws.sorted) return fail(GND_ERR_STATE, "workspace has no cell-ordered point buffer");
+    a.offc = ctx->vws.offc; a.sorted = ctx->vws.sorted;
+    int64_t warps = (int64_t)batch * ((ctx->nx * ctx->ny + 31) / 32);
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 8) blocks = 148 * 8;
     pfn_scatter_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);

@@ -22,6 +22,7 @@
 #include "voxelize.cuh"
 #include <limits.h>
 #include <math.h>
+#include <stdlib.h>
 
 namespace gnd {
 
@@ -126,6 +127,93 @@ __global__ void __launch_bounds__(256) vox_rank_kernel(const VoxArgs a) {
     for (int c = tid; c < a.cells; c += 256) hist[c] = s_tbl[c];
 }
 
+// Tile-parallel exact ranking (grids up to VOX_RT_MAX_CELLS cells).  A tile is 8 warps x 224 consecutive
+// points; every warp ranks ITS 224 points in input order (7 steps of 32: match.any inside the step, a
+// private byte counter per cell across steps), all warps at once.  The eight byte counters of a cell sit in
+// one 8-byte word, so a single shared-memory load gives a point the counts of the warps in front of it
+// (its rank inside the tile) and the tile total; `s_run` carries the per-cell count over the chunk's tiles.
+// Outputs are identical to vox_rank_kernel's: cell[i], chunk-local rank, chunk histogram, atomicMin(first).
+__device__ __forceinline__ unsigned byte_sum64(uint2 v) { return __vsadu4(v.x, 0u) + __vsadu4(v.y, 0u); }
+
+__global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const VoxArgs a) {
+    extern __shared__ __align__(16) unsigned char s_rt[];
+    uint2 *s_cnt = reinterpret_cast<uint2 *>(s_rt);                         // [cells] byte w = points warp w saw in this tile
+    uint16_t *s_run = reinterpret_cast<uint16_t *>(s_cnt + a.cells);        // [cells] points seen in earlier tiles of the chunk
+    const int b = blockIdx.x / a.K, k = blockIdx.x % a.K;
+    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int start = k * a.T;
+    const int end = min(start + a.T, n);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)b * a.N;
+    int32_t *first = a.ws.first + (int64_t)b * a.cells;
+
+    for (int c = tid; c < a.cells; c += VOX_RT_WARPS * 32) { s_cnt[c] = make_uint2(0u, 0u); s_run[c] = 0; }
+    __syncthreads();
+
+    const uint2 below = warp == 0 ? make_uint2(0u, 0u)
+                      : warp < 4  ? make_uint2(0xffffffffu >> (32 - 8 * warp), 0u)
+                      : warp == 4 ? make_uint2(0xffffffffu, 0u)
+                                  : make_uint2(0xffffffffu, 0xffffffffu >> (32 - 8 * (warp - 4)));
+    for (int t0 = start; t0 < end; t0 += VOX_RT_TILE) {
+        const int wbase = t0 + warp * (VOX_RT_STEPS * 32);
+        int c[VOX_RT_STEPS], r[VOX_RT_STEPS];
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {                 // all loads of the tile in flight at once
+            const int i = wbase + s * 32 + lane;
+            c[s] = (i < end) ? point_cell(a, a.points + (base + i) * a.F) : -1;
+        }
+        // phase A: in-order ranking inside the warp's 224 points
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
+            const unsigned act = __ballot_sync(0xffffffffu, c[s] >= 0);
+            r[s] = 0;
+            if (c[s] >= 0) {
+                const unsigned peers = __match_any_sync(act, c[s]);
+                const int leader = __ffs(peers) - 1;
+                unsigned seen = 0;
+                unsigned char *cnt = reinterpret_cast<unsigned char *>(s_cnt + c[s]) + warp;
+                if (lane == leader) { seen = *cnt; *cnt = (unsigned char)(seen + __popc(peers)); }
+                seen = __shfl_sync(peers, seen, leader);
+                r[s] = (int)seen + __popc(peers & lanemask_lt());
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        // phase B: rank inside the tile = counts of the warps in front + rank inside the warp
+        int run[VOX_RT_STEPS], tot[VOX_RT_STEPS];
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
+            const int i = wbase + s * 32 + lane;
+            run[s] = -1; tot[s] = 0;
+            if (c[s] >= 0) {
+                const uint2 v = s_cnt[c[s]];
+                const int pre = (int)byte_sum64(make_uint2(v.x & below.x, v.y & below.y));
+                const int rs = (int)s_run[c[s]];
+                if (pre + r[s] == 0) { run[s] = rs; tot[s] = (int)byte_sum64(v); }    // first point of its cell in the tile
+                r[s] += pre + rs;
+            }
+            if (i < end) {
+                a.ws.cell[base + i] = c[s];
+                a.ws.lrank[base + i] = (uint16_t)r[s];
+            }
+        }
+        __syncthreads();
+        // phase C: the cell's first point of the tile folds the tile into the chunk state and clears the counters
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
+            if (run[s] >= 0) {
+                if (run[s] == 0) atomicMin(&first[c[s]], wbase + s * 32 + lane);
+                s_run[c[s]] = (uint16_t)(run[s] + tot[s]);
+                s_cnt[c[s]] = make_uint2(0u, 0u);
+            }
+        }
+        __syncthreads();
+    }
+    uint32_t *hist = a.ws.hist + ((int64_t)b * a.K + k) * a.cells;
+    for (int c = tid; c < a.cells; c += VOX_RT_WARPS * 32) hist[c] = s_run[c];
+}
+
+
 __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     extern __shared__ uint32_t s_bm[];             // bit i set <=> point i is the first point of a cell
     __shared__ int s_tpre[1024];
@@ -140,6 +228,7 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     int32_t *coors = a.coors + (int64_t)b * a.max_voxels * 3;
     int32_t *num = a.num_points + (int64_t)b * a.max_voxels;
     int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
+    int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
 
     for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
     if (tid == 0) s_cut = INT_MAX;
@@ -183,14 +272,22 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     const int cut = s_cut;
     const int kcut = (cut < n) ? cut / a.T : a.K;
 
-    // chunk histograms -> exclusive prefixes over chunks; points per voxel before truncation
+    // chunk histograms -> exclusive prefixes over chunks; points per voxel before truncation.
+    // (loads first, stores after: the K loads of a cell are independent and stay in flight together)
     for (int c = tid; c < a.cells; c += 1024) {
         uint32_t run = 0, before_cut = 0;
-        for (int k = 0; k < a.K; ++k) {
-            uint32_t h = hist[(int64_t)k * a.cells + c];
-            hist[(int64_t)k * a.cells + c] = run;
-            if (k == kcut) before_cut = run;
-            run += h;
+        for (int k0 = 0; k0 < a.K; k0 += 8) {
+            uint32_t h[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) h[j] = (k0 + j < a.K) ? hist[(int64_t)(k0 + j) * a.cells + c] : 0u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (k0 + j < a.K) {
+                    hist[(int64_t)(k0 + j) * a.cells + c] = run;
+                    if (k0 + j == kcut) before_cut = run;
+                    run += h[j];
+                }
+            }
         }
         const int v = vid[c];
         if (v >= 0) num[v] = (cut < n) ? (int)before_cut : (int)run;
@@ -204,17 +301,33 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
         }
         __syncthreads();
     }
-    // truncate (:49-52) and build the CSR offsets of the pillar point lists
-    const int segM = (M + 1023) / 1024;
-    int lsum = 0;
-    for (int v = tid * segM; v < min((tid + 1) * segM, M); ++v) {
-        int c = min(num[v], a.max_points);
-        num[v] = c;
-        lsum += c;
+    // truncate (:49-52); CSR offsets of the kept points in CELL order (what the pillar encoder walks)
+    int carry = 0;
+    for (int c0 = 0; c0 < a.cells; c0 += 1024) {
+        const int c = c0 + tid;
+        int kept = 0;
+        if (c < a.cells) {
+            const int v = vid[c];
+            if (v >= 0) { kept = min(num[v], a.max_points); num[v] = kept; }
+        }
+        int tot;
+        const int ex = block_exclusive_scan(kept, s_warp, &tot);
+        if (c < a.cells) offc[c] = carry + ex;
+        carry += tot;
     }
-    int S;
-    int run = block_exclusive_scan(lsum, s_warp, &S);
-    for (int v = tid * segM; v < min((tid + 1) * segM, M); ++v) { off[v] = run; run += num[v]; }
+    if (tid == 0) offc[a.cells] = carry;
+    const int S = carry;
+    __syncthreads();
+    // ... and in VOXEL order (the pillar lists of the drop-in API)
+    carry = 0;
+    for (int v0 = 0; v0 < M; v0 += 1024) {
+        const int v = v0 + tid;
+        const int kept = (v < M) ? num[v] : 0;
+        int tot;
+        const int ex = block_exclusive_scan(kept, s_warp, &tot);
+        if (v < M) off[v] = carry + ex;
+        carry += tot;
+    }
     if (tid == 0) {
         off[M] = S;
         a.voxel_count[b] = M;
@@ -238,6 +351,14 @@ __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
                 if (r < a.max_points) {
                     slot = v * a.max_points + r;
                     a.list[(int64_t)b * a.N + a.offsets[(int64_t)b * (a.max_voxels + 1) + v] + r] = i;
+                    if (a.ws.sorted) {
+                        const float *src = a.points + gi * a.F;
+                        float4 pt;
+                        if (a.vec4) pt = __ldg(reinterpret_cast<const float4 *>(src));
+                        else pt = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), a.F > 3 ? __ldg(src + 3) : 0.0f);
+                        if (a.apply_shift) pt.z = __fadd_rn(pt.z, a.z_shift);
+                        a.ws.sorted[(int64_t)b * a.N + a.ws.offc[(int64_t)b * (a.cells + 1) + c] + r] = pt;
+                    }
                     if (a.voxels) {
                         const float *src = a.points + gi * a.F;
                         float *dst = a.voxels + (((int64_t)b * a.max_voxels + v) * a.max_points + r) * a.F;
@@ -287,23 +408,27 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     if (cells > 100000) return fail(GND_ERR_UNSUPPORTED, "voxel grid of %lld cells > 100000 (shared-memory cell table)", (long long)cells);
     if (n_points > 1600000) return fail(GND_ERR_UNSUPPORTED, "%lld points per scan > 1600000 (shared-memory first-point bitmap)", (long long)n_points);
     plan->cells = (int32_t)cells;
+    plan->tiled = (cells <= VOX_RT_MAX_CELLS && !getenv("GNDNET_VOX_SERIAL")) ? 1 : 0;
+    const int64_t sub = plan->tiled ? VOX_RT_TILE : VOX_SUB;
     int64_t n = n_points < 1 ? 1 : n_points;
     int64_t kmin = (n + VOX_MAX_T - 1) / VOX_MAX_T;
-    int64_t kmax = (n + VOX_SUB - 1) / VOX_SUB;
-    int64_t k = (2 * 148 + batch - 1) / batch;              // about two CTAs per SM over the batch
+    int64_t kmax = (n + sub - 1) / sub;
+    // tiled: two CTAs per SM in ONE wave (floor); serial: about two CTAs per SM over the batch
+    int64_t k = plan->tiled ? (2 * 148) / batch : (2 * 148 + batch - 1) / batch;
+    if (k < 1) k = 1;
     if (k > VOX_MAX_K) k = VOX_MAX_K;
     if (k > kmax) k = kmax;
     if (k < kmin) k = kmin;
     int64_t t = (n + k - 1) / k;
-    t = (t + VOX_SUB - 1) / VOX_SUB * VOX_SUB;
+    t = (t + sub - 1) / sub * sub;
     plan->T = (int32_t)t;
     plan->K = (int32_t)((n + t - 1) / t);
-    plan->rank_smem = (size_t)plan->cells * sizeof(uint16_t);
+    plan->rank_smem = plan->tiled ? (size_t)plan->cells * (sizeof(uint2) + sizeof(uint16_t)) : (size_t)plan->cells * sizeof(uint16_t);
     plan->assign_smem = (size_t)((n_points + 31) / 32 + 1) * sizeof(uint32_t);
     return GND_OK;
 }
 
-size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out) {
+size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out, bool with_sorted) {
     Carver c(ws);
     VoxWs w;
     size_t bn = (size_t)batch * (size_t)(n_points < 1 ? 1 : n_points);
@@ -313,6 +438,8 @@ size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws,
     w.hist = c.take<uint32_t>((size_t)batch * plan.K * plan.cells);
     w.vid = c.take<int32_t>((size_t)batch * plan.cells);
     w.cutoff = c.take<int32_t>((size_t)batch);
+    w.offc = c.take<int32_t>((size_t)batch * (plan.cells + 1));
+    w.sorted = with_sorted ? c.take<float4>(bn) : nullptr;
     if (out) *out = w;
     return c.bytes();
 }
@@ -338,8 +465,14 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     GND_CUDA_CHECK(cudaFuncSetAttribute(vox_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
     GND_CUDA_CHECK(cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * plan.cells * sizeof(int32_t), stream));
     if (n_points > 0) {
-        vox_rank_kernel<<<batch * plan.K, 256, plan.rank_smem, stream>>>(a);
-        GND_LAUNCH_CHECK("vox_rank_kernel");
+        if (plan.tiled) {
+            GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            vox_rank_tiles_kernel<<<batch * plan.K, VOX_RT_WARPS * 32, plan.rank_smem, stream>>>(a);
+            GND_LAUNCH_CHECK("vox_rank_tiles_kernel");
+        } else {
+            vox_rank_kernel<<<batch * plan.K, 256, plan.rank_smem, stream>>>(a);
+            GND_LAUNCH_CHECK("vox_rank_kernel");
+        }
     } else {
         GND_CUDA_CHECK(cudaMemsetAsync(ws.hist, 0, (size_t)batch * plan.K * plan.cells * sizeof(uint32_t), stream));
     }

@@ -7,12 +7,18 @@ namespace gnd {
 constexpr int VOX_SUB = 2048;        // points ranked per sub-tile of a chunk
 constexpr int VOX_MAX_T = 61440;     // chunk size limit: chunk-local counts are uint16
 constexpr int VOX_MAX_K = 64;        // chunks per scan
+// tile-parallel ranker: 8 warps x 7 steps x 32 points per tile (per-warp byte counters hold <= 224)
+constexpr int VOX_RT_WARPS = 8;
+constexpr int VOX_RT_STEPS = 7;
+constexpr int VOX_RT_TILE = VOX_RT_WARPS * VOX_RT_STEPS * 32;
+constexpr int VOX_RT_MAX_CELLS = 11264;   // 10 bytes of shared memory per cell, two CTAs per SM
 
 struct VoxPlan {
     int32_t grid[3];     // nx, ny, nz   (utils/point_cloud_ops.py:24-27)
     int32_t cells;       // nx*ny*nz
     int32_t K;           // chunks per scan
     int32_t T;           // points per chunk (multiple of VOX_SUB)
+    int32_t tiled;       // 1: vox_rank_tiles_kernel (grids <= VOX_RT_MAX_CELLS cells), 0: vox_rank_kernel
     size_t rank_smem;    // dynamic smem of the rank kernel
     size_t assign_smem;  // dynamic smem of the assign kernel
 };
@@ -25,10 +31,12 @@ struct VoxWs {
     uint32_t *hist;      // [B][K][cells] chunk histogram -> exclusive prefix over chunks (in place)
     int32_t *vid;        // [B][cells]  voxel id of the cell, -1 if none
     int32_t *cutoff;     // [B]         first dropped index when max_voxels overflows, else INT_MAX
+    int32_t *offc;       // [B][cells+1] CSR offsets of the kept points in CELL order (pillar-encode input)
+    float4 *sorted;      // [B][N]      kept points (x, y, z [+shift], r) grouped by cell, slot order inside; may be null
 };
 
 int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, VoxPlan *plan);
-size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out);
+size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out, bool with_sorted = false);
 int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
             const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
             int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,
