@@ -17,6 +17,7 @@
 // 128/256-byte NHWC row -- and empty cells get their zeros from the same kernel, so the canvas needs
 // no separate memset.  HBM-bound: <= 16 B read per kept point + 64*e B written per cell.
 #include "model.cuh"
+#include <math.h>
 
 namespace gnd {
 
@@ -38,6 +39,7 @@ struct PfnArgs {
     // fused inputs: kept points grouped by cell (voxelize.cu)
     const int32_t *offc;
     const float4 *sorted;
+    float zmid, q_xy, iq_xy, q_z, iq_z;   // fixed-point scales of the pillar-mean reduction
     // dense inputs
     const float *coors4, *num_f;
     int64_t M;
@@ -120,10 +122,14 @@ __device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s
 // pillar centre so that a point costs 4 multiply-adds per channel instead of 9:
 //   W f + b = A x' + B y' + C z + D r (+ Wd |p|) + E,   x' = x - cx,  y' = y - cy,
 //   A = w_x + w_dmx + w_dcx,  B = w_y + w_dmy + w_dcy,  C = w_z + w_dmz,  D = w_r,
-//   E = b + w_x cx + w_y cy + w_dmx (cx - mean_x) + w_dmy (cy - mean_y) - w_dmz mean_z     (per pillar)
+//   E = b + w_x cx + w_y cy - w_dmx mean(x') - w_dmy mean(y') - w_dmz mean(z)            (per pillar)
 // and relu(max_p(t_p + E)) = relu(max_p t_p + E).  All products stay below |w| in magnitude except E, whose
 // rounding (|w| * 50 m * 2^-24) is the same as the reference's own w_x * x term.
-__global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnArgs a) {
+// The pillar mean (:120) is taken over cell-relative coordinates in fixed point (2^-k units chosen on the
+// host so that max_points * half a voxel fits 31 bits): one integer warp reduction (redux.sync) per axis
+// instead of a 5-level float shuffle tree, and an error (<= 2^-25 of a voxel per point) far below the float32
+// summation error of the reference's own mean.
+__global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_kernel(const PfnArgs a) {
     __shared__ float4 s_pt[PFN_WARPS][32];
     __shared__ float s_dist[PFN_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -139,6 +145,7 @@ __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnAr
     const float D0 = kf == 4 ? W(3, ch0) : 0.0f, D1 = kf == 4 ? W(3, ch1) : 0.0f;
     const float G0 = a.with_distance ? W(kf + 5, ch0) : 0.0f, G1 = a.with_distance ? W(kf + 5, ch1) : 0.0f;
     const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
+    const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
     const int cells = a.nx * a.ny;
     const int groups = (cells + 31) / 32;
     const int64_t total = (int64_t)a.B * groups;
@@ -150,36 +157,41 @@ __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnAr
         const int my_o = __ldg(offc + cl);
         const int my_n = __ldg(offc + min(cl + 1, cells)) - my_o;
         const int ncell = min(32, cells - c0);
-        for (int j = 0; j < ncell; ++j) {
+        int cx = c0 % a.nx, cy = c0 / a.nx;
+        int64_t oidx = ((int64_t)b * cells + c0) * PFN_OUT + 2 * lane;
+        for (int j = 0; j < ncell; ++j, ++cx, oidx += PFN_OUT) {
+            if (cx == a.nx) { cx = 0; ++cy; }
             const int n = __shfl_sync(0xffffffffu, my_n, j);
-            const int o = __shfl_sync(0xffffffffu, my_o, j);
-            const int c = c0 + j;
             float m0 = 0.0f, m1 = 0.0f;
             if (n > 0) {
-                // :120 points_mean = sum over the pillar's slots / num_points
-                float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (lane < n) p0 = __ldg(pts + o + lane);
-                float sx = p0.x, sy = p0.y, sz = p0.z;
-                for (int q = 32 + lane; q < n; q += 32) { const float4 p = __ldg(pts + o + q); sx += p.x; sy += p.y; sz += p.z; }
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) {
-                    sx += __shfl_xor_sync(0xffffffffu, sx, d);
-                    sy += __shfl_xor_sync(0xffffffffu, sy, d);
-                    sz += __shfl_xor_sync(0xffffffffu, sz, d);
-                }
-                const float nf = (float)n;
-                const float mx = __fdiv_rn(sx, nf), my = __fdiv_rn(sy, nf), mz = __fdiv_rn(sz, nf);
+                const int o = __shfl_sync(0xffffffffu, my_o, j);
                 // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
-                const float pcx = __fadd_rn(__fmul_rn((float)(c % a.nx), a.vx), a.xoff);
-                const float pcy = __fadd_rn(__fmul_rn((float)(c / a.nx), a.vy), a.yoff);
-                const float dmx = pcx - mx, dmy = pcy - my;
-                const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(wmx0, dmx, fmaf(wmy0, dmy, fmaf(-wmz0, mz, b0)))));
-                const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(wmx1, dmx, fmaf(wmy1, dmy, fmaf(-wmz1, mz, b1)))));
+                const float pcx = __fadd_rn(__fmul_rn((float)cx, a.vx), a.xoff);
+                const float pcy = __fadd_rn(__fmul_rn((float)cy, a.vy), a.yoff);
+                float4 p0 = make_float4(pcx, pcy, a.zmid, 0.f);
+                if (lane < n) p0 = __ldg(pts + o + lane);
+                const float4 f0 = make_float4(p0.x - pcx, p0.y - pcy, p0.z, p0.w);
+                int qx = __float2int_rn(f0.x * a.q_xy), qy = __float2int_rn(f0.y * a.q_xy), qz = __float2int_rn((p0.z - a.zmid) * a.q_z);
+                for (int q = 32 + lane; q < n; q += 32) {
+                    const float4 p = __ldg(pts + o + q);
+                    qx += __float2int_rn((p.x - pcx) * a.q_xy); qy += __float2int_rn((p.y - pcy) * a.q_xy);
+                    qz += __float2int_rn((p.z - a.zmid) * a.q_z);
+                }
+                qx = __reduce_add_sync(0xffffffffu, qx);
+                qy = __reduce_add_sync(0xffffffffu, qy);
+                qz = __reduce_add_sync(0xffffffffu, qz);
+                const float rn = __frcp_rn((float)n);
+                const float mxr = (float)qx * (rn * a.iq_xy), myr = (float)qy * (rn * a.iq_xy);   // mean(x') , mean(y')
+                const float mz = a.zmid + (float)qz * (rn * a.iq_z);
+                const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(-wmx0, mxr, fmaf(-wmy0, myr, fmaf(-wmz0, mz, b0)))));
+                const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(-wmx1, mxr, fmaf(-wmy1, myr, fmaf(-wmz1, mz, b1)))));
                 float t0 = -INFINITY, t1 = -INFINITY;
                 for (int q0 = 0; q0 < n; q0 += 32) {
                     if (q0 + lane < n) {
-                        const float4 p = (q0 == 0) ? p0 : __ldg(pts + o + q0 + lane);
-                        s_pt[warp][lane] = make_float4(p.x - pcx, p.y - pcy, p.z, p.w);
+                        float4 f = f0;
+                        float4 p = p0;
+                        if (q0 != 0) { p = __ldg(pts + o + q0 + lane); f = make_float4(p.x - pcx, p.y - pcy, p.z, p.w); }
+                        s_pt[warp][lane] = f;
                         if (a.with_distance) s_dist[warp][lane] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p.x, p.x), __fmul_rn(p.y, p.y)), __fmul_rn(p.z, p.z)));
                     }
                     __syncwarp();
@@ -201,12 +213,20 @@ __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_kernel(const PfnAr
                     }
                     __syncwarp();
                 }
-                m0 = fmaxf(t0 + E0, 0.0f);
-                m1 = fmaxf(t1 + E1, 0.0f);
                 // padded slots give relu(b') (:137-140 then :54-58)
-                if (n < a.P) { m0 = fmaxf(m0, b0); m1 = fmaxf(m1, b1); }
+                m0 = fmaxf(t0 + E0, n < a.P ? rb0 : 0.0f);
+                m1 = fmaxf(t1 + E1, n < a.P ? rb1 : 0.0f);
             }
-            store_cell(a, (int64_t)b * cells + c, lane, m0, m1);
+            if (a.out32) {
+                *reinterpret_cast<float2 *>(a.out32 + oidx) = make_float2(m0, m1);
+            } else {
+                const __half2 hh = __floats2half2_rn(m0, m1);
+                *reinterpret_cast<__half2 *>(a.out_hi + oidx) = hh;
+                if (a.out_lo) {
+                    const float2 back = __half22float2(hh);
+                    *reinterpret_cast<__half2 *>(a.out_lo + oidx) = __floats2half2_rn(m0 - back.x, m1 - back.y);
+                }
+            }
         }
     }
 }
@@ -279,6 +299,17 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     a.apply_shift = 1; a.z_shift = ctx->cfg.lidar_height;
     if (!ctx->vws.sorted) return fail(GND_ERR_STATE, "workspace has no cell-ordered point buffer");
     a.offc = ctx->vws.offc; a.sorted = ctx->vws.sorted;
+    {
+        // kept points lie inside their voxel: |x'|, |y'| <= voxel/2 (+ rounding), |z - zmid| <= z extent / 2
+        const gnd_config &c = ctx->cfg;
+        const double hxy = 0.5 * (c.voxel_size_f64[0] > c.voxel_size_f64[1] ? c.voxel_size_f64[0] : c.voxel_size_f64[1]) * 1.01 + 1e-3;
+        const double hz = 0.5 * (c.pc_range_f64[5] - c.pc_range_f64[2]) * 1.01 + 1e-3;
+        const double lim = 1073741824.0 / (double)(c.max_points_voxel > 32 ? c.max_points_voxel : 32);
+        int e;
+        frexp(lim / hxy, &e); a.q_xy = (float)ldexp(1.0, e - 1); a.iq_xy = (float)ldexp(1.0, 1 - e);
+        frexp(lim / hz, &e); a.q_z = (float)ldexp(1.0, e - 1); a.iq_z = (float)ldexp(1.0, 1 - e);
+        a.zmid = (float)(0.5 * (c.pc_range_f64[5] + c.pc_range_f64[2]));
+    }
     int64_t warps = (int64_t)batch * ((ctx->nx * ctx->ny + 31) / 32);
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 8) blocks = 148 * 8;

@@ -34,6 +34,7 @@ struct VoxArgs {
     int32_t F;
     int32_t vec4;          // rows are 16-byte aligned float4
     float lo[3], vs[3];
+    float inv[3];          // exact reciprocal when voxel_size is a power of two (then x / vs == x * inv bit for bit), else 0
     int32_t grid[3];       // nx ny nz
     int32_t cells;
     int32_t K, T;
@@ -49,26 +50,35 @@ struct VoxArgs {
 // utils/point_cloud_ops.py:34-37: c = floor((p - lo) / vs) in IEEE float32 (subtract, then true divide),
 // rejected when c < 0 or c >= grid.  NaN compares false on both of the reference's tests (UB there);
 // here it is rejected.
-__device__ __forceinline__ int axis_cell(float p, float lo, float vs, int grid) {
-    float c = floorf(__fdiv_rn(__fsub_rn(p, lo), vs));
+__device__ __forceinline__ int axis_cell(float p, float lo, float vs, float inv, int grid) {
+    const float d = __fsub_rn(p, lo);
+    float c = floorf(inv != 0.0f ? __fmul_rn(d, inv) : __fdiv_rn(d, vs));
     if (!(c >= 0.0f) || !(c < (float)grid)) return -1;
     return (int)c;
 }
 
-__device__ __forceinline__ int point_cell(const VoxArgs &a, const float *row) {
-    float x, y, z;
+__device__ __forceinline__ void load_xyz(const VoxArgs &a, const float *row, float &x, float &y, float &z) {
     if (a.vec4) {
         float4 v = __ldg(reinterpret_cast<const float4 *>(row));
         x = v.x; y = v.y; z = v.z;
     } else {
         x = __ldg(row); y = __ldg(row + 1); z = __ldg(row + 2);
     }
+}
+
+__device__ __forceinline__ int xyz_cell(const VoxArgs &a, float x, float y, float z) {
     if (a.apply_shift) z = __fadd_rn(z, a.z_shift);   // predict_ground.py:104-107
-    int cx = axis_cell(x, a.lo[0], a.vs[0], a.grid[0]);
-    int cy = axis_cell(y, a.lo[1], a.vs[1], a.grid[1]);
-    int cz = axis_cell(z, a.lo[2], a.vs[2], a.grid[2]);
+    int cx = axis_cell(x, a.lo[0], a.vs[0], a.inv[0], a.grid[0]);
+    int cy = axis_cell(y, a.lo[1], a.vs[1], a.inv[1], a.grid[1]);
+    int cz = axis_cell(z, a.lo[2], a.vs[2], a.inv[2], a.grid[2]);
     if ((cx | cy | cz) < 0) return -1;
     return (cz * a.grid[1] + cy) * a.grid[0] + cx;
+}
+
+__device__ __forceinline__ int point_cell(const VoxArgs &a, const float *row) {
+    float x, y, z;
+    load_xyz(a, row, x, y, z);
+    return xyz_cell(a, x, y, z);
 }
 
 __global__ void __launch_bounds__(256) vox_rank_kernel(const VoxArgs a) {
@@ -154,13 +164,26 @@ __global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const
                       : warp < 4  ? make_uint2(0xffffffffu >> (32 - 8 * warp), 0u)
                       : warp == 4 ? make_uint2(0xffffffffu, 0u)
                                   : make_uint2(0xffffffffu, 0xffffffffu >> (32 - 8 * (warp - 4)));
+    // the next tile's coordinates are fetched while this tile is ranked
+    float px[VOX_RT_STEPS], py[VOX_RT_STEPS], pz[VOX_RT_STEPS];
+#pragma unroll
+    for (int s = 0; s < VOX_RT_STEPS; ++s) {
+        const int i = start + warp * (VOX_RT_STEPS * 32) + s * 32 + lane;
+        px[s] = py[s] = pz[s] = 0.0f;
+        if (i < end) load_xyz(a, a.points + (base + i) * a.F, px[s], py[s], pz[s]);
+    }
     for (int t0 = start; t0 < end; t0 += VOX_RT_TILE) {
         const int wbase = t0 + warp * (VOX_RT_STEPS * 32);
         int c[VOX_RT_STEPS], r[VOX_RT_STEPS];
 #pragma unroll
-        for (int s = 0; s < VOX_RT_STEPS; ++s) {                 // all loads of the tile in flight at once
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
             const int i = wbase + s * 32 + lane;
-            c[s] = (i < end) ? point_cell(a, a.points + (base + i) * a.F) : -1;
+            c[s] = (i < end) ? xyz_cell(a, px[s], py[s], pz[s]) : -1;
+        }
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
+            const int i = wbase + VOX_RT_TILE + s * 32 + lane;
+            if (i < end) load_xyz(a, a.points + (base + i) * a.F, px[s], py[s], pz[s]);
         }
         // phase A: in-order ranking inside the warp's 224 points
 #pragma unroll
@@ -249,6 +272,8 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
 
     // voxel id = number of cells whose first point comes earlier (:42-48); break index (:44-45)
     const int nx = a.grid[0], ny = a.grid[1];
+    int cx = tid % nx, cyz = tid / nx;                 // c = cyz * nx + cx, advanced by 1024 per iteration
+    const int step_x = 1024 % nx, step_yz = 1024 / nx;
     for (int c = tid; c < a.cells; c += 1024) {
         int f = first[c];
         int v = -1;
@@ -259,7 +284,7 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
             r += __popc(s_bm[w] & ((1u << (f & 31)) - 1u));
             if (r < a.max_voxels) {
                 v = r;
-                const int cx = c % nx, cy = (c / nx) % ny, cz = c / (nx * ny);
+                const int cy = (a.grid[2] == 1) ? cyz : cyz % ny, cz = (a.grid[2] == 1) ? 0 : cyz / ny;
                 if (a.reverse) { coors[v * 3 + 0] = cz; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cx; }
                 else           { coors[v * 3 + 0] = cx; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cz; }
             } else if (r == a.max_voxels) {
@@ -267,6 +292,8 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
             }
         }
         vid[c] = v;
+        cx += step_x; cyz += step_yz;
+        if (cx >= nx) { cx -= nx; ++cyz; }
     }
     __syncthreads();
     const int cut = s_cut;
@@ -301,33 +328,31 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
         }
         __syncthreads();
     }
-    // truncate (:49-52); CSR offsets of the kept points in CELL order (what the pillar encoder walks)
-    int carry = 0;
-    for (int c0 = 0; c0 < a.cells; c0 += 1024) {
-        const int c = c0 + tid;
-        int kept = 0;
-        if (c < a.cells) {
-            const int v = vid[c];
-            if (v >= 0) { kept = min(num[v], a.max_points); num[v] = kept; }
-        }
-        int tot;
-        const int ex = block_exclusive_scan(kept, s_warp, &tot);
-        if (c < a.cells) offc[c] = carry + ex;
-        carry += tot;
+    // truncate (:49-52); CSR offsets of the kept points in CELL order (what the pillar encoder walks).
+    // Each thread owns a run of consecutive cells: one block scan instead of one per 1024 cells.
+    const int cpt = (a.cells + 1023) / 1024;
+    const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
+    int lsum = 0;
+    for (int c = cbeg; c < cend; ++c) {
+        const int v = vid[c];
+        if (v >= 0) { const int kept = min(num[v], a.max_points); num[v] = kept; lsum += kept; }
     }
-    if (tid == 0) offc[a.cells] = carry;
-    const int S = carry;
-    __syncthreads();
+    int S;
+    int run = block_exclusive_scan(lsum, s_warp, &S);
+    for (int c = cbeg; c < cend; ++c) {
+        offc[c] = run;
+        const int v = vid[c];
+        if (v >= 0) run += num[v];
+    }
+    if (tid == 0) offc[a.cells] = S;
     // ... and in VOXEL order (the pillar lists of the drop-in API)
-    carry = 0;
-    for (int v0 = 0; v0 < M; v0 += 1024) {
-        const int v = v0 + tid;
-        const int kept = (v < M) ? num[v] : 0;
-        int tot;
-        const int ex = block_exclusive_scan(kept, s_warp, &tot);
-        if (v < M) off[v] = carry + ex;
-        carry += tot;
-    }
+    const int vpt = (M + 1023) / 1024;
+    const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
+    lsum = 0;
+    for (int v = vbeg; v < vend; ++v) lsum += num[v];
+    int S2;
+    run = block_exclusive_scan(lsum, s_warp, &S2);
+    for (int v = vbeg; v < vend; ++v) { off[v] = run; run += num[v]; }
     if (tid == 0) {
         off[M] = S;
         a.voxel_count[b] = M;
@@ -335,29 +360,36 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     }
 }
 
+// grid.y = (scan, chunk): no per-point divisions; grid.x strides over the chunk's points
 __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
-    const int64_t total = (int64_t)a.B * a.N;
-    for (int64_t gi = (int64_t)blockIdx.x * 256 + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * 256) {
-        const int b = (int)(gi / a.N), i = (int)(gi - (int64_t)b * a.N);
-        const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int b = blockIdx.y / a.K, k = blockIdx.y - b * a.K;
+    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int cstart = k * a.T, cend = min(cstart + a.T, a.N);
+    const int cut = a.ws.cutoff[b];
+    const int64_t base = (int64_t)b * a.N;
+    const int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
+    const uint32_t *pre = a.ws.hist + ((int64_t)b * a.K + k) * a.cells;
+    const int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
+    const int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
+    for (int i = cstart + blockIdx.x * 256 + threadIdx.x; i < cend; i += gridDim.x * 256) {
+        const int64_t gi = base + i;
         if (i >= n) { if (a.slot) a.slot[gi] = -1; continue; }
         const int c = a.ws.cell[gi];
         int slot = -1;
-        if (c >= 0 && i < a.ws.cutoff[b]) {
-            const int v = a.ws.vid[(int64_t)b * a.cells + c];
+        if (c >= 0 && i < cut) {
+            const int v = __ldg(vid + c);
             if (v >= 0) {
-                const int k = i / a.T;
-                const int r = (int)a.ws.lrank[gi] + (int)a.ws.hist[((int64_t)b * a.K + k) * a.cells + c];
+                const int r = (int)a.ws.lrank[gi] + (int)__ldg(pre + c);
                 if (r < a.max_points) {
                     slot = v * a.max_points + r;
-                    a.list[(int64_t)b * a.N + a.offsets[(int64_t)b * (a.max_voxels + 1) + v] + r] = i;
+                    a.list[base + __ldg(off + v) + r] = i;
                     if (a.ws.sorted) {
                         const float *src = a.points + gi * a.F;
                         float4 pt;
                         if (a.vec4) pt = __ldg(reinterpret_cast<const float4 *>(src));
                         else pt = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), a.F > 3 ? __ldg(src + 3) : 0.0f);
                         if (a.apply_shift) pt.z = __fadd_rn(pt.z, a.z_shift);
-                        a.ws.sorted[(int64_t)b * a.N + a.ws.offc[(int64_t)b * (a.cells + 1) + c] + r] = pt;
+                        a.ws.sorted[base + __ldg(offc + c) + r] = pt;
                     }
                     if (a.voxels) {
                         const float *src = a.points + gi * a.F;
@@ -454,7 +486,12 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     VoxArgs a;
     a.points = points; a.counts = counts; a.B = batch; a.N = (int32_t)n_points; a.F = p->num_features;
     a.vec4 = (p->num_features == 4 && ((uintptr_t)points % 16) == 0) ? 1 : 0;
-    for (int j = 0; j < 3; ++j) { a.lo[j] = p->coors_range[j]; a.vs[j] = p->voxel_size[j]; a.grid[j] = plan.grid[j]; }
+    for (int j = 0; j < 3; ++j) {
+        a.lo[j] = p->coors_range[j]; a.vs[j] = p->voxel_size[j]; a.grid[j] = plan.grid[j];
+        int e = 0;
+        const float m = frexpf(a.vs[j], &e);
+        a.inv[j] = (m == 0.5f && e > -100 && e < 100) ? 1.0f / a.vs[j] : 0.0f;
+    }
     a.cells = plan.cells; a.K = plan.K; a.T = plan.T;
     a.apply_shift = p->apply_z_shift; a.z_shift = p->z_shift;
     a.max_points = p->max_points; a.max_voxels = p->max_voxels; a.reverse = p->reverse_index;
@@ -479,10 +516,11 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     vox_assign_kernel<<<batch, 1024, plan.assign_smem, stream>>>(a);
     GND_LAUNCH_CHECK("vox_assign_kernel");
     if (n_points > 0) {
-        int64_t total = (int64_t)batch * n_points;
-        int blocks = (int)((total + 255) / 256);
-        if (blocks > 148 * 32) blocks = 148 * 32;
-        vox_scatter_kernel<<<blocks, 256, 0, stream>>>(a);
+        int gx = (plan.T + 255) / 256;
+        const int want = (148 * 16 + batch * plan.K - 1) / (batch * plan.K);     // ~16 CTAs per SM over the grid
+        if (gx > want) gx = want;
+        if (gx < 1) gx = 1;
+        vox_scatter_kernel<<<dim3(gx, batch * plan.K), 256, 0, stream>>>(a);
         GND_LAUNCH_CHECK("vox_scatter_kernel");
     }
     return GND_OK;
