@@ -105,6 +105,7 @@ extern "C" int gnd_workspace_bytes(const gnd_ctx *cctx, int32_t batch, int64_t n
     gnd_ctx tmp = *cctx;     // sizes only; never touches device memory
     tmp.tmaps = nullptr;
     tmp.hmaps = nullptr;
+    tmp.h2maps = nullptr;
     int rc = vox_make_plan(&tmp.vparams, batch, n_points, &tmp.vplan);
     if (rc != GND_OK) return rc;
     *h_bytes = carve_all(&tmp, batch, n_points, nullptr, nullptr) + 1024;

@@ -320,17 +320,21 @@ int tc_build_tensor_maps(gnd_ctx *ctx) {
     t.built = true;
     const Act *ins[8];
     for (int l = 0; l < 8; ++l) ins[l] = layer_input(ctx, l);
-    return halo_build(ctx, ins);
+    int rc = halo_build(ctx, ins);
+    if (rc != GND_OK) return rc;
+    return halo2_build(ctx, ins);
 }
 
 void tc_free_tensor_maps(gnd_ctx *ctx) {
     delete ctx->tmaps;
     ctx->tmaps = nullptr;
     halo_free(ctx);
+    halo2_free(ctx);
 }
 
 int tc_conv_run(gnd_ctx *ctx, int l, const Act &in, const Act &out, int B, bool fuse_regressor, cudaStream_t st) {
     if (!ctx->tmaps || !ctx->tmaps->built) return fail(GND_ERR_STATE, "tensor maps not built (bind the workspace after loading weights)");
+    if (halo2_usable(ctx, l)) return halo2_conv_run(ctx, l, out, B, fuse_regressor, st);
     if (halo_usable(ctx, l)) return halo_conv_run(ctx, l, out, B, fuse_regressor, st);
     const TensorMaps &t = *ctx->tmaps;
     const ConvLayer &L = ctx->conv[l];

@@ -34,6 +34,7 @@ struct ConvLayer {
 
 struct TensorMaps;   // conv_tc.cu
 struct HaloMaps;     // conv_halo.cu
+struct Halo2Maps;    // conv_halo2.cu
 
 }  // namespace gnd
 
@@ -67,6 +68,7 @@ struct gnd_ctx {
     float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
     gnd::TensorMaps *tmaps = nullptr;
     gnd::HaloMaps *hmaps = nullptr;
+    gnd::Halo2Maps *h2maps = nullptr;
 
     int last_launches = 0;
 };
@@ -88,6 +90,11 @@ int halo_build(gnd_ctx *ctx, const Act *const inputs[8]);
 void halo_free(gnd_ctx *ctx);
 bool halo_usable(const gnd_ctx *ctx, int layer);
 int halo_conv_run(gnd_ctx *ctx, int layer, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
+// conv_halo2.cu (the same on a CTA pair, tcgen05 cta_group::2)
+int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]);
+void halo2_free(gnd_ctx *ctx);
+bool halo2_usable(const gnd_ctx *ctx, int layer);
+int halo2_conv_run(gnd_ctx *ctx, int layer, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
 // segment.cu
 int segment_run(const gnd_segment_params *p, float *points, const int32_t *counts, int32_t batch,
                 int64_t n_points, const float *elevation, double *labels_f64, int8_t *labels_i8,

@@ -17,6 +17,9 @@
 #ifndef RB
 #define RB 128
 #endif
+#ifndef DSTK
+#define DSTK 0
+#endif
 #ifndef NBV
 #define NBV 64
 #endif
@@ -68,7 +71,7 @@ __global__ void __launch_bounds__(128, 1) probe(const __grid_constant__ CUtensor
     extern __shared__ uint8_t raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     // [0, 1024) slack | A: ROWS*128 B | slack 8 KB | B: NB*128 | barriers
-    uint8_t *sA = smem + 1024;
+    uint8_t *sA = smem + 1024 + DSTK * RB;   // TMA destination: DSTK rows past a 1024-byte boundary
     uint8_t *sB = sA + ROWS * RB + 8192;
     uint64_t *bars = reinterpret_cast<uint64_t *>(sB + NB * RB);
     uint32_t *tslot = reinterpret_cast<uint32_t *>(bars + 2);
