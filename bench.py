@@ -55,7 +55,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -112,19 +112,22 @@ def cpu_path_scan(sd, cfg, raw):
     return t3 - t0, (t1 - t0, t2 - t1, t3 - t2)
 
 
-def cpu_baseline(n_scans, warm=1):
+def cpu_baseline(seconds, warm=2, pool=16):
+    """The CPU path on a bounded sample: distinct synthetic scans (a pool of `pool`, cycled) until `seconds`
+    of CPU work have been timed."""
     import torch
     from oracle import synth
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
-    scans = [synth.hdl64_scan(9000 + i) for i in range(n_scans + warm)]
+    scans = [synth.hdl64_scan(9000 + i) for i in range(pool)]
     for s in scans[:warm]:
         cpu_path_scan(sd, cfg, s)
     times, parts = [], np.zeros(3)
-    for s in scans[warm:]:
-        t, p = cpu_path_scan(sd, cfg, s)
+    while sum(times) < seconds:
+        t, p = cpu_path_scan(sd, cfg, scans[len(times) % pool])
         times.append(t)
         parts += np.array(p)
+    n_scans = len(times)
     total = float(np.sum(times))
     return {"value": n_scans / total, "unit": "scans/s", "cores": int(torch.get_num_threads()), "kind": "port",
             "sample": "%d synthetic HDL-64 scans of %d points, batch 1, %.1f s of CPU work (voxelize %.0f%% / torch-CPU "
@@ -136,25 +139,28 @@ def run_reference(args, rank):
     if rank != 0:
         return
     cfgd = {"workload": "GndNet kittiSem inference, synthetic 120k-point HDL-64 scans, streaming batch %d per GPU" % args.batch,
-            "points_per_scan": N_POINTS, "batch_per_gpu": args.batch, "sample_per_step": "1 scan"}
+            "points_per_scan": N_POINTS, "batch_per_gpu": args.batch,
+            "sample_per_step": "%d scans of the batch (bounded sample), one at a time like predict_ground.py" % args.ref_scans_per_step}
     from oracle import synth
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
-    scans = [synth.hdl64_scan(9000 + i) for i in range(args.warmup + args.steps)]
-    for s in scans[:args.warmup]:
-        cpu_path_scan(sd, cfg, s)
+    per = args.ref_scans_per_step
+    pool = [synth.hdl64_scan(9000 + i) for i in range(16)]
+    k = 0
+    for _ in range(args.warmup):
+        cpu_path_scan(sd, cfg, pool[k % 16]); k += 1
     t0 = time.perf_counter()
-    for s in scans[args.warmup:]:
-        cpu_path_scan(sd, cfg, s)
+    for _ in range(args.steps * per):
+        cpu_path_scan(sd, cfg, pool[k % 16]); k += 1
     total = time.perf_counter() - t0
     import torch
-    v = args.steps / total
+    v = args.steps * per / total
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "scans/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfgd,
             "cpu_baseline": {"value": v, "unit": "scans/s", "cores": int(torch.get_num_threads()), "kind": "port",
-                             "sample": "%d steps of 1 scan (oracle port of the reference CPU path: C voxelize + torch-CPU "
-                                       "forward + C segment); checkpoint %s" % (args.steps, ck)},
+                             "sample": "%d steps x %d scans (oracle port of the reference CPU path: C voxelize + torch-CPU "
+                                       "forward + C segment); checkpoint %s" % (args.steps, args.ref_scans_per_step, ck)},
             "e2e": {"value": v, "unit": "scans/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -167,19 +173,22 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("GNDNET_PRECISION", "mixed"))
     ap.add_argument("--batch", type=int, default=64, help="scans per step per GPU")
-    ap.add_argument("--cpu-scans", type=int, default=8)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work timed for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-scans-per-step", type=int, default=8, help="--impl reference: scans timed per step (bounded sample of the batch)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        args.steps = args.steps or 8
+        args.steps = args.steps or 20
+        if args.steps * args.ref_scans_per_step > 4000:      # keep the arm within a few minutes at ~25 scans/s
+            args.ref_scans_per_step = max(1, 4000 // args.steps)
         args.warmup = 1 if args.warmup is None else max(1, args.warmup)
         run_reference(args, rank)
         return
-    args.steps = args.steps or 20
-    args.warmup = 3 if args.warmup is None else max(3, args.warmup)
+    args.steps = args.steps or 200            # ~0.5 s timed region: long enough for the power-capped clocks to settle
+    args.warmup = 5 if args.warmup is None else max(3, args.warmup)
 
     import torch
     import torch.distributed as dist
@@ -285,7 +294,7 @@ def main():
                              "peak_source": pk["src"] + " sustained bf16 (kernel timed inside a long step)",
                              "launch_ms_avg": conv_ms / 8.0}
         if not args.no_cpu_baseline:
-            extra["cpu_baseline"], _ = cpu_baseline(args.cpu_scans)
+            extra["cpu_baseline"], _ = cpu_baseline(args.cpu_seconds)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "scans/s", "n_gpus": world, "steps": args.steps,

@@ -459,7 +459,8 @@ int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
         p.n_ntiles = L.cout / p.NT;
         const int planes = L.split ? 2 : 1;
         int NR = 0;
-        if (!h2_geometry(in.H, in.W, p.RB, planes, p.MT, p.NT, 6, &p, &NR) &&
+        const int want_sb = getenv("GNDNET_H2_MINSB") ? atoi(getenv("GNDNET_H2_MINSB")) : 6;
+        if (!h2_geometry(in.H, in.W, p.RB, planes, p.MT, p.NT, want_sb, &p, &NR) &&
             !h2_geometry(in.H, in.W, p.RB, planes, p.MT, p.NT, 4, &p, &NR))
             continue;
         p.H = in.H; p.W = in.W; p.Cout = L.cout; p.B = ctx->B;

@@ -341,7 +341,7 @@ class GroundEstimatorNet(nn.Module):
             conv += np.array(list(cms))
         out = {k: v / reps for k, v in acc.items()}
         out["conv_layers_ms"] = [float(x) / reps for x in conv]
-        out["conv_kernel"] = "conv3x3_f32_kernel" if self.precision == "fp32" else "conv3x3_tc_kernel"
+        out["conv_kernel"] = "conv3x3_f32_kernel" if self.precision == "fp32" else "conv3x3_halo2_kernel"
         return out
 
     def pillars(self, batch):
