@@ -62,8 +62,9 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
     }
     uint8_t *idx1 = c.take<uint8_t>((size_t)B * H1 * W1 * 128);
     float *regpart = (prec == GND_PREC_FP32) ? nullptr : c.take<float>((size_t)B * H * W * 9);
+    int32_t *pfn_ctr = c.take<int32_t>(4);
     if (ws) {
-        ctx->idx1 = idx1; ctx->regpart = regpart;
+        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr;
         if (names) {
             names->push_back({"idx1", idx1, (size_t)B * H1 * W1 * 128});
             if (regpart) names->push_back({"regpart", regpart, (size_t)B * H * W * 9 * 4});
@@ -124,6 +125,7 @@ extern "C" int gnd_bind_workspace(gnd_ctx *ctx, void *workspace, size_t bytes, i
     if (rc != GND_OK) return rc;
     ctx->ws = workspace; ctx->ws_bytes = bytes; ctx->B = batch; ctx->N = n_points;
     carve_all(ctx, batch, n_points, workspace, nullptr);
+    GND_CUDA_CHECK(cudaMemset(ctx->pfn_ctr, 0, 4 * sizeof(int32_t)));
     if (ctx->cfg.precision != GND_PREC_FP32 && ctx->weights_loaded) {
         rc = tc_build_tensor_maps(ctx);
         if (rc != GND_OK) { ctx->ws = nullptr; return rc; }

@@ -66,6 +66,7 @@ struct gnd_ctx {
     gnd::Act canvas, d1a, d1b, p1, d2a, d2b, u2, u2a, u2b, u1, u1a, u1b;
     uint8_t *idx1 = nullptr;   // [B][H1][W1][128] argmax (0..3) of down1's pool
     float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
+    int32_t *pfn_ctr = nullptr; // [2] work-queue head + finished-CTA count of pfn_scatter_kernel (self-resetting)
     gnd::TensorMaps *tmaps = nullptr;
     gnd::HaloMaps *hmaps = nullptr;
     gnd::Halo2Maps *h2maps = nullptr;

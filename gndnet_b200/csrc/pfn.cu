@@ -43,6 +43,7 @@ struct PfnArgs {
     // dense inputs
     const float *coors4, *num_f;
     int64_t M;
+    int32_t *ctr;               // fused: [0] next group of cells to hand out, [1] CTAs finished (last one clears both)
     // output canvas [B][ny][nx][64]
     float *out32;
     __half *out_hi, *out_lo;
@@ -129,7 +130,7 @@ __device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s
 // host so that max_points * half a voxel fits 31 bits): one integer warp reduction (redux.sync) per axis
 // instead of a 5-level float shuffle tree, and an error (<= 2^-25 of a voxel per point) far below the float32
 // summation error of the reference's own mean.
-__global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_kernel(const PfnArgs a) {
+__global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const PfnArgs a) {
     __shared__ float4 s_pt[PFN_WARPS][32];
     __shared__ float s_dist[PFN_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -148,9 +149,15 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_kernel(const Pf
     const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
     const int cells = a.nx * a.ny;
     const int groups = (cells + 31) / 32;
-    const int64_t total = (int64_t)a.B * groups;
-    for (int64_t g = (int64_t)blockIdx.x * PFN_WARPS + warp; g < total; g += (int64_t)gridDim.x * PFN_WARPS) {
-        const int b = (int)(g / groups), c0 = (int)(g - (int64_t)b * groups) * 32;
+    const int total = a.B * groups;
+    // groups are handed out through a device counter: the points per group vary from 0 to 32 * max_points,
+    // so a static split leaves most warps idle behind the few that drew the dense cells next to the sensor
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = atomicAdd(a.ctr, 1);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= total) break;
+        const int b = g / groups, c0 = (g - b * groups) * 32;
         const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
         const float4 *pts = a.sorted + (int64_t)b * a.N;
         const int cl = min(c0 + lane, cells);
@@ -229,6 +236,11 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_kernel(const Pf
             }
         }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(a.ctr + 1, 1) == (int)gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; __threadfence(); }
+    }
 }
 
 // Drop-in tensors (model.py:36-42): voxels [M][P][F], coors [M][4] float (b,z,y,x), num_points [M] float.
@@ -298,7 +310,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     a.points = points; a.N = n_points;
     a.apply_shift = 1; a.z_shift = ctx->cfg.lidar_height;
     if (!ctx->vws.sorted) return fail(GND_ERR_STATE, "workspace has no cell-ordered point buffer");
-    a.offc = ctx->vws.offc; a.sorted = ctx->vws.sorted;
+    a.offc = ctx->vws.offc; a.sorted = ctx->vws.sorted; a.ctr = ctx->pfn_ctr;
     {
         // kept points lie inside their voxel: |x'|, |y'| <= voxel/2 (+ rounding), |z - zmid| <= z extent / 2
         const gnd_config &c = ctx->cfg;
@@ -312,7 +324,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     }
     int64_t warps = (int64_t)batch * ((ctx->nx * ctx->ny + 31) / 32);
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically
     pfn_scatter_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);
     GND_LAUNCH_CHECK("pfn_scatter_kernel");
     return GND_OK;
