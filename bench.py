@@ -269,16 +269,46 @@ def main():
         l1 = torch.empty((1, N_POINTS), dtype=torch.int8, device=dev)
         lat = []
         with torch.no_grad():
-            for i in range(30):
+            for i in range(1030):
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
                 model.infer(one, threshold=0.08, out=(h1, l1))
                 b.record()
                 torch.cuda.synchronize()
-                if i >= 5:
+                if i >= 30:
                     lat.append(a.elapsed_time(b))
         extra["latency_ms_p50_batch1"] = float(np.median(lat))
         extra["latency_ms_p95_batch1"] = float(np.percentile(lat, 95))
+        # the same scan through a CUDA-graph replay of the 17 launches (gndnet_b200.pipeline.GraphedInfer), resident
+        # input, and with the 1.92 MB pinned H2D + D2H of the map and labels inside the timed region
+        from gndnet_b200.pipeline import GraphedInfer
+        gi = GraphedInfer(model, 1, N_POINTS, threshold=0.08, labels="int8")
+        gi.points.copy_(one)
+        hp = pinned[0][:1]
+        hh = torch.empty((1, model.ny, model.nx), dtype=torch.float32).pin_memory()
+        hl = torch.empty((1, N_POINTS), dtype=torch.int8).pin_memory()
+        lat_g, lat_h = [], []
+        with torch.no_grad():
+            for i in range(1030):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                gi()
+                b.record()
+                torch.cuda.synchronize()
+                if i >= 30:
+                    lat_g.append(a.elapsed_time(b))
+            for i in range(230):
+                t0 = time.perf_counter()
+                gi(hp)
+                hh.copy_(gi.height, non_blocking=True)
+                hl.copy_(gi.labels, non_blocking=True)
+                torch.cuda.synchronize()
+                if i >= 30:
+                    lat_h.append(1e3 * (time.perf_counter() - t0))
+        extra["latency_ms_p50_batch1_graph"] = float(np.median(lat_g))
+        extra["latency_ms_p95_batch1_graph"] = float(np.percentile(lat_g, 95))
+        extra["latency_ms_p50_batch1_host_to_host"] = float(np.median(lat_h))
+        extra["latency_ms_p95_batch1_host_to_host"] = float(np.percentile(lat_h, 95))
         # restore the batch binding and time the stages of one step with events
         with torch.no_grad():
             model.infer(resident[0], threshold=0.08, out=(height, labels))

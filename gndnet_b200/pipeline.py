@@ -70,3 +70,43 @@ class ScanStream:
         s = self.slots[slot]
         s["ev_out"].synchronize()
         return s["h_height"], s["h_labels"]
+
+
+class GraphedInfer:
+    """The fused path (gnd_infer: ~17 kernels) captured once into a CUDA graph and replayed per scan batch.
+
+    For the batch-1 latency case (BASELINE.json configs[1]; ros_node.py's one-cloud-at-a-time loop) the launch
+    overhead of 17 back-to-back enqueues is a third of the device time; a replay is one launch.  The graph is
+    bound to fixed buffers: write the scan(s) into ``self.points`` (or pass them to ``__call__``, which copies
+    on the current stream), results appear in ``self.height`` / ``self.labels``.
+    """
+
+    def __init__(self, model, batch, n_points, threshold=0.08, labels="int8"):
+        dev = model._device()
+        self.model, self.dev = model, dev
+        F = model.cfg.input_features
+        ldt = {"int8": torch.int8, "float64": torch.float64}[labels]
+        with torch.cuda.device(dev), torch.no_grad():
+            self.points = torch.zeros((batch, n_points, F), dtype=torch.float32, device=dev)
+            self.height = torch.empty((batch, model.ny, model.nx), dtype=torch.float32, device=dev)
+            self.labels = torch.empty((batch, n_points), dtype=ldt, device=dev)
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):             # binds the workspace / uploads weights outside the capture
+                model.infer(self.points, threshold=threshold, out=(self.height, self.labels))
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                model.infer(self.points, threshold=threshold, out=(self.height, self.labels))
+            self.launches = model.launches
+            self._bound = model._bound
+            self._wver = model._weights_version
+
+    def __call__(self, points=None):
+        if self.model._bound != self._bound or self.model._params_version() != self._wver:
+            raise RuntimeError("the model's workspace or weights changed after the graph was captured; build a new GraphedInfer")
+        if points is not None:
+            self.points.copy_(points.reshape(self.points.shape), non_blocking=True)
+        self.graph.replay()
+        return self.height, self.labels

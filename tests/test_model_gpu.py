@@ -157,3 +157,23 @@ def test_model_requires_cuda_and_loud_errors(cuda):
     m = m.cuda().eval()
     with pytest.raises((ValueError, GndError)):
         m(torch.zeros(2, 100, 3).cuda(), torch.zeros(2, 4).cuda(), torch.ones(2).cuda())
+
+
+@pytest.mark.parametrize("batch", [1, 3])
+def test_graph_replay_equals_direct_infer(batch, cuda):
+    """GraphedInfer (one CUDA-graph launch) must give the bytes the 17 direct enqueues give, replay after replay,
+    also when the scan in its input buffer changes between replays."""
+    from gndnet_b200.pipeline import GraphedInfer
+    cfg = synth.make_cfg("kitti", batch_size=batch)
+    model, sd = helpers.load_model(cfg, "kitti", "mixed", cuda)
+    n = 30000
+    scans = [np.stack([synth.hdl64_scan(40 + 7 * k + b)[::4] for b in range(batch)]) for k in range(3)]
+    gi = GraphedInfer(model, batch, n, threshold=0.08, labels="int8")
+    assert gi.launches > 0
+    with torch.no_grad():
+        for k in (0, 1, 2, 0):
+            pts = torch.from_numpy(scans[k]).cuda()
+            h_g, l_g = gi(pts)
+            h_g, l_g = h_g.clone(), l_g.clone()
+            h_d, l_d = model.infer(pts, threshold=0.08, labels="int8")
+            assert torch.equal(h_g, h_d) and torch.equal(l_g, l_d)
