@@ -43,6 +43,7 @@ struct PfnArgs {
     // dense inputs
     const float *coors4, *num_f;
     int64_t M;
+    int32_t gshift;             // fused: a work unit is 2^gshift consecutive cells (<= 32)
     int32_t *ctr;               // fused: [0] next group of cells to hand out, [1] CTAs finished (last one clears both)
     // output canvas [B][ny][nx][64]
     float *out32;
@@ -148,7 +149,8 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
     const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
     const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
     const int cells = a.nx * a.ny;
-    const int groups = (cells + 31) / 32;
+    const int gsize = 1 << a.gshift;
+    const int groups = (cells + gsize - 1) >> a.gshift;
     const int total = a.B * groups;
     // groups are handed out through a device counter: the points per group vary from 0 to 32 * max_points,
     // so a static split leaves most warps idle behind the few that drew the dense cells next to the sensor
@@ -157,13 +159,13 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
         if (lane == 0) g = atomicAdd(a.ctr, 1);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= total) break;
-        const int b = g / groups, c0 = (g - b * groups) * 32;
+        const int b = g / groups, c0 = (g - b * groups) << a.gshift;
         const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
         const float4 *pts = a.sorted + (int64_t)b * a.N;
         const int cl = min(c0 + lane, cells);
         const int my_o = __ldg(offc + cl);
         const int my_n = __ldg(offc + min(cl + 1, cells)) - my_o;
-        const int ncell = min(32, cells - c0);
+        const int ncell = min(gsize, cells - c0);
         int cx = c0 % a.nx, cy = c0 / a.nx;
         int64_t oidx = ((int64_t)b * cells + c0) * PFN_OUT + 2 * lane;
         for (int j = 0; j < ncell; ++j, ++cx, oidx += PFN_OUT) {
@@ -322,7 +324,12 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
         frexp(lim / hz, &e); a.q_z = (float)ldexp(1.0, e - 1); a.iq_z = (float)ldexp(1.0, 1 - e);
         a.zmid = (float)(0.5 * (c.pc_range_f64[5] + c.pc_range_f64[2]));
     }
-    int64_t warps = (int64_t)batch * ((ctx->nx * ctx->ny + 31) / 32);
+    // unit size: 32 cells when that still leaves >= 4 units per resident warp (big batches), smaller otherwise so
+    // that a single scan spreads over the whole GPU and one dense cell, not 32 of them, is the tail
+    const int64_t cells_all = (int64_t)batch * ctx->nx * ctx->ny;
+    a.gshift = 5;
+    while (a.gshift > 0 && (cells_all >> a.gshift) < 4 * 148 * 4 * PFN_WARPS) --a.gshift;
+    int64_t warps = (cells_all + (1 << a.gshift) - 1) >> a.gshift;
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically
     pfn_scatter_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);

@@ -449,6 +449,7 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     int64_t k = plan->tiled ? (2 * 148) / batch : (2 * 148 + batch - 1) / batch;
     if (k < 1) k = 1;
     if (k > VOX_MAX_K) k = VOX_MAX_K;
+    if (const char *e = getenv("GNDNET_VOX_K")) { int v = atoi(e); if (v > 0 && v < k) k = v; }
     if (k > kmax) k = kmax;
     if (k < kmin) k = kmin;
     int64_t t = (n + k - 1) / k;
