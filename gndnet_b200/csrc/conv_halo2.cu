@@ -54,7 +54,9 @@ struct Halo2Layer {
 };
 
 struct Halo2Maps {
-    Halo2Layer layer[8];
+    Halo2Layer layer[8];     // throughput geometry: the widest N tile, 512 TMEM columns in use
+    Halo2Layer small[8];     // latency geometry for small batches: N tile of 64 (or $GNDNET_H2_SMALL_NT), one M tile per item,
+                             // so that a single scan already spreads over most of the 74 CTA pairs
 };
 
 struct Half { int b, sx0, q0, r_lo, tiles; };
@@ -442,8 +444,11 @@ static bool h2_geometry(int H, int W, int RB, int planes, int MT, int NT, int mi
 
 int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
     if (!ctx->h2maps) ctx->h2maps = new Halo2Maps();
-    for (int l = 0; l < 8; ++l) {
-        Halo2Layer &hl = ctx->h2maps->layer[l];
+    const int small_nt = getenv("GNDNET_H2_SMALL_NT") ? atoi(getenv("GNDNET_H2_SMALL_NT")) : 64;
+    for (int l2 = 0; l2 < 16; ++l2) {
+        const int l = l2 >> 1;
+        const bool small = (l2 & 1) != 0;
+        Halo2Layer &hl = small ? ctx->h2maps->small[l] : ctx->h2maps->layer[l];
         hl.usable = false;
         const ConvLayer &L = ctx->conv[l];
         const Act &in = *inputs[l];
@@ -454,8 +459,9 @@ int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
         p.kc = p.RB / 2; p.ksteps = p.RB / 32;
         p.cblocks = L.cin / p.kc;
         p.NT = L.cout < 128 ? 64 : (L.cout % 256 == 0 ? 256 : 128);
-        if (L.cout % p.NT != 0) continue;
-        p.MT = 256 / p.NT;
+        if (small) p.NT = small_nt < p.NT ? small_nt : p.NT;
+        if (p.NT < 32 || p.NT % 32 != 0 || L.cout % p.NT != 0) continue;
+        p.MT = small ? 1 : 256 / p.NT;
         p.n_ntiles = L.cout / p.NT;
         const int planes = L.split ? 2 : 1;
         int NR = 0;
@@ -487,8 +493,8 @@ int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
         hl.p = p;
         hl.usable = true;
         if (getenv("GNDNET_DEBUG"))
-            fprintf(stderr, "halo2 layer %d: %dx%d cin %d cout %d split %d | Wp %d strips %d tiles/strip %d MT %d NT %d NR %d SB %d row0 %d smem %zu\n",
-                    l, in.H, in.W, L.cin, L.cout, L.split, p.Wp, p.strips, p.tiles_per_strip, p.MT, p.NT, NR, p.SB, p.row0, hl.smem);
+            fprintf(stderr, "halo2 layer %d%s: %dx%d cin %d cout %d split %d | Wp %d strips %d tiles/strip %d MT %d NT %d NR %d SB %d row0 %d smem %zu\n",
+                    l, small ? " (small-batch)" : "", in.H, in.W, L.cin, L.cout, L.split, p.Wp, p.strips, p.tiles_per_strip, p.MT, p.NT, NR, p.SB, p.row0, hl.smem);
     }
     return GND_OK;
 }
@@ -505,7 +511,19 @@ bool halo2_usable(const gnd_ctx *ctx, int l) {
 }
 
 int halo2_conv_run(gnd_ctx *ctx, int l, const Act &out, int B, bool fuse_regressor, cudaStream_t st) {
-    const Halo2Layer &hl = ctx->h2maps->layer[l];
+    // geometry: the throughput one unless it leaves most of the 74 pairs without work
+    const Halo2Layer *pick = &ctx->h2maps->layer[l];
+    {
+        const Halo2Layer &sm = ctx->h2maps->small[l];
+        auto items = [&](const Halo2Params &q) { return ((B * q.strips * q.groups + 1) / 2) * q.n_ntiles; };
+        const char *force = getenv("GNDNET_H2_GEOM");             // "big" / "small": A/B timing and tests
+        // (an N tile of 64 re-reads the halo once per N tile and runs the MMAs at the shared-memory limit: it pays only
+        //  while the wide geometry leaves about half of the pairs idle -- measured at batch 1, 2 and 4)
+        if (sm.usable && ((items(pick->p) <= 40 && items(sm.p) > items(pick->p)) || (force && force[0] == 's'))
+            && !(force && force[0] == 'b'))
+            pick = &sm;
+    }
+    const Halo2Layer &hl = *pick;
     Halo2Params p = hl.p;
     p.B = B;
     p.half_items = B * p.strips * p.groups;

@@ -177,3 +177,20 @@ def test_graph_replay_equals_direct_infer(batch, cuda):
             h_g, l_g = h_g.clone(), l_g.clone()
             h_d, l_d = model.infer(pts, threshold=0.08, labels="int8")
             assert torch.equal(h_g, h_d) and torch.equal(l_g, l_d)
+
+
+@pytest.mark.parametrize("cfgname,scan", [("kitti", "hdl64_s0"), ("camera", "small_camera")])
+def test_conv_geometries_agree(cfgname, scan, cuda, monkeypatch):
+    """The throughput geometry (widest N tile) and the small-batch geometry (N tile 64, one M tile per item) of
+    the tcgen05 convolution accumulate every output in the same K order: the height maps must be bit-identical."""
+    cfg = synth.make_cfg(cfgname, batch_size=1)
+    model, sd = helpers.load_model(cfg, cfgname, "mixed", cuda)
+    raw = cases.load_case(scan)[1]
+    pts = torch.from_numpy(raw).cuda()
+    outs = {}
+    with torch.no_grad():
+        for geom in ("big", "small"):
+            monkeypatch.setenv("GNDNET_H2_GEOM", geom)
+            h, _ = model.infer(pts, threshold=0.08, labels="int8")
+            outs[geom] = h.clone()
+    assert torch.equal(outs["big"], outs["small"])
