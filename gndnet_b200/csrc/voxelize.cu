@@ -37,7 +37,7 @@ struct VoxArgs {
     float inv[3];          // exact reciprocal when voxel_size is a power of two (then x / vs == x * inv bit for bit), else 0
     int32_t grid[3];       // nx ny nz
     int32_t cells;
-    int32_t K, T;
+    int32_t K, T, G;
     int32_t apply_shift;
     float z_shift;
     int32_t max_points, max_voxels, reverse;
@@ -237,12 +237,18 @@ __global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const
 }
 
 
+// G CTAs per scan.  Every CTA rebuilds the first-point bitmap and its popcount prefix (cheap: one load per
+// cell), then ranks / prefixes / truncates only ITS slice of the cells; the CTA that finishes last for a scan
+// turns the per-cell and per-voxel kept counts into the two CSR offset arrays.
+constexpr int VOX_DONE_BASE = 0x7f7f7f7f;     // `done` shares the 0x7f memset of `first`
+
 __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     extern __shared__ uint32_t s_bm[];             // bit i set <=> point i is the first point of a cell
     __shared__ int s_tpre[1024];
     __shared__ int s_warp[33];
-    __shared__ int s_cut;
-    const int b = blockIdx.x, tid = threadIdx.x;
+    __shared__ int s_cut, s_last;
+    const int G = a.G;
+    const int b = blockIdx.x / G, part = blockIdx.x - b * G, tid = threadIdx.x;
     const int n = a.counts ? min(a.counts[b], a.N) : a.N;
     const int nW = (n + 31) >> 5;
     const int32_t *first = a.ws.first + (int64_t)b * a.cells;
@@ -267,15 +273,35 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     int n_occ;
     int pre = block_exclusive_scan(local, s_warp, &n_occ);
     s_tpre[tid] = pre;
-    __syncthreads();
     const int M = min(n_occ, a.max_voxels);
+    // break index (:44-45): the first point of the cell whose rank is max_voxels, i.e. set bit number max_voxels
+    if (n_occ > a.max_voxels && pre <= a.max_voxels && a.max_voxels < pre + local) {
+        int r = pre;
+        for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) {
+            uint32_t m = s_bm[w];
+            const int pc = __popc(m);
+            if (r + pc > a.max_voxels) {
+                for (int k = a.max_voxels - r; k > 0; --k) m &= m - 1;
+                s_cut = w * 32 + __ffs(m) - 1;
+                break;
+            }
+            r += pc;
+        }
+    }
+    __syncthreads();
+    const int cut = s_cut;
+    const int kcut = (cut < n) ? cut / a.T : a.K;
+    const bool overflow = cut < n;
 
-    // voxel id = number of cells whose first point comes earlier (:42-48); break index (:44-45)
+    // this CTA's slice of the cells
+    const int per = (a.cells + G - 1) / G;
+    const int c_lo = min(part * per, a.cells), c_hi = min(c_lo + per, a.cells);
     const int nx = a.grid[0], ny = a.grid[1];
-    int cx = tid % nx, cyz = tid / nx;                 // c = cyz * nx + cx, advanced by 1024 per iteration
+    int cx = (c_lo + tid) % nx, cyz = (c_lo + tid) / nx;          // c = cyz * nx + cx, advanced by 1024 per iteration
     const int step_x = 1024 % nx, step_yz = 1024 / nx;
-    for (int c = tid; c < a.cells; c += 1024) {
-        int f = first[c];
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        // voxel id = number of cells whose first point comes earlier (:42-48)
+        const int f = first[c];
         int v = -1;
         if (f < n) {
             const int w = f >> 5, t = w / seg;
@@ -287,21 +313,13 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
                 const int cy = (a.grid[2] == 1) ? cyz : cyz % ny, cz = (a.grid[2] == 1) ? 0 : cyz / ny;
                 if (a.reverse) { coors[v * 3 + 0] = cz; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cx; }
                 else           { coors[v * 3 + 0] = cx; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cz; }
-            } else if (r == a.max_voxels) {
-                s_cut = f;
             }
         }
         vid[c] = v;
         cx += step_x; cyz += step_yz;
         if (cx >= nx) { cx -= nx; ++cyz; }
-    }
-    __syncthreads();
-    const int cut = s_cut;
-    const int kcut = (cut < n) ? cut / a.T : a.K;
-
-    // chunk histograms -> exclusive prefixes over chunks; points per voxel before truncation.
-    // (loads first, stores after: the K loads of a cell are independent and stay in flight together)
-    for (int c = tid; c < a.cells; c += 1024) {
+        // chunk histograms -> exclusive prefixes over chunks; points of the cell before the break index.
+        // (loads first, stores after: the K loads of a cell are independent and stay in flight together)
         uint32_t run = 0, before_cut = 0;
         for (int k0 = 0; k0 < a.K; k0 += 8) {
             uint32_t h[8];
@@ -316,47 +334,68 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
                 }
             }
         }
-        const int v = vid[c];
-        if (v >= 0) num[v] = (cut < n) ? (int)before_cut : (int)run;
+        if (!overflow) {          // truncate (:49-52) right here: kept points of the cell / voxel
+            const int kept = (v >= 0) ? min((int)run, a.max_points) : 0;
+            if (v >= 0) num[v] = kept;
+            offc[c] = kept;
+        } else if (v >= 0) {
+            num[v] = (int)before_cut;
+        }
     }
-    __syncthreads();
-    if (cut < n) {   // overflow: add the points of the break chunk that precede the break index
+    if (overflow) {   // add the points of the break chunk that precede the break index, then truncate
+        __syncthreads();
         const int32_t *cell = a.ws.cell + (int64_t)b * a.N;
         for (int j = kcut * a.T + tid; j < cut; j += 1024) {
-            int c = cell[j];
-            if (c >= 0) { int v = vid[c]; if (v >= 0) atomicAdd(&num[v], 1); }
+            const int c = cell[j];
+            if (c >= c_lo && c < c_hi) { const int v = vid[c]; if (v >= 0) atomicAdd(&num[v], 1); }
         }
         __syncthreads();
+        for (int c = c_lo + tid; c < c_hi; c += 1024) {
+            const int v = vid[c];
+            int kept = 0;
+            if (v >= 0) { kept = min(num[v], a.max_points); num[v] = kept; }
+            offc[c] = kept;
+        }
     }
-    // truncate (:49-52); CSR offsets of the kept points in CELL order (what the pillar encoder walks).
+    if (G > 1) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            int32_t *done = a.ws.done + b;
+            const int t = atomicAdd(done, 1);
+            s_last = (t == VOX_DONE_BASE + G - 1);
+            if (s_last) *done = VOX_DONE_BASE;
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) return;
+    } else {
+        __syncthreads();
+    }
+    // CSR offsets of the kept points in CELL order (what the pillar encoder walks), in place over the kept counts.
     // Each thread owns a run of consecutive cells: one block scan instead of one per 1024 cells.
-    const int cpt = (a.cells + 1023) / 1024;
-    const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
-    int lsum = 0;
-    for (int c = cbeg; c < cend; ++c) {
-        const int v = vid[c];
-        if (v >= 0) { const int kept = min(num[v], a.max_points); num[v] = kept; lsum += kept; }
-    }
-    int S;
-    int run = block_exclusive_scan(lsum, s_warp, &S);
-    for (int c = cbeg; c < cend; ++c) {
-        offc[c] = run;
-        const int v = vid[c];
-        if (v >= 0) run += num[v];
-    }
-    if (tid == 0) offc[a.cells] = S;
-    // ... and in VOXEL order (the pillar lists of the drop-in API)
-    const int vpt = (M + 1023) / 1024;
-    const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
-    lsum = 0;
-    for (int v = vbeg; v < vend; ++v) lsum += num[v];
-    int S2;
-    run = block_exclusive_scan(lsum, s_warp, &S2);
-    for (int v = vbeg; v < vend; ++v) { off[v] = run; run += num[v]; }
-    if (tid == 0) {
-        off[M] = S;
-        a.voxel_count[b] = M;
-        a.ws.cutoff[b] = cut;
+    {
+        const int cpt = (a.cells + 1023) / 1024;
+        const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
+        int lsum = 0;
+        for (int c = cbeg; c < cend; ++c) lsum += __ldcg(offc + c);
+        int S;
+        int run = block_exclusive_scan(lsum, s_warp, &S);
+        for (int c = cbeg; c < cend; ++c) { const int k = __ldcg(offc + c); offc[c] = run; run += k; }
+        if (tid == 0) offc[a.cells] = S;
+        // ... and in VOXEL order (the pillar lists of the drop-in API)
+        const int vpt = (M + 1023) / 1024;
+        const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
+        lsum = 0;
+        for (int v = vbeg; v < vend; ++v) lsum += __ldcg(num + v);
+        int S2;
+        run = block_exclusive_scan(lsum, s_warp, &S2);
+        for (int v = vbeg; v < vend; ++v) { off[v] = run; run += __ldcg(num + v); }
+        if (tid == 0) {
+            off[M] = S;
+            a.voxel_count[b] = M;
+            a.ws.cutoff[b] = cut;
+        }
     }
 }
 
@@ -456,6 +495,11 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     t = (t + sub - 1) / sub * sub;
     plan->T = (int32_t)t;
     plan->K = (int32_t)((n + t - 1) / t);
+    {   // assign CTAs per scan: about two per SM over the batch, at most 16
+        int g = (2 * 148) / batch;
+        if (const char *e = getenv("GNDNET_VOX_G")) g = atoi(e);
+        plan->G = g < 1 ? 1 : (g > 16 ? 16 : g);
+    }
     plan->rank_smem = plan->tiled ? (size_t)plan->cells * (sizeof(uint2) + sizeof(uint16_t)) : (size_t)plan->cells * sizeof(uint16_t);
     plan->assign_smem = (size_t)((n_points + 31) / 32 + 1) * sizeof(uint32_t);
     return GND_OK;
@@ -467,7 +511,8 @@ size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws,
     size_t bn = (size_t)batch * (size_t)(n_points < 1 ? 1 : n_points);
     w.cell = c.take<int32_t>(bn);
     w.lrank = c.take<uint16_t>(bn);
-    w.first = c.take<int32_t>((size_t)batch * plan.cells);
+    w.first = c.take<int32_t>((size_t)batch * plan.cells + (size_t)batch);    // + done[B], same 0x7f fill
+    w.done = w.first ? w.first + (size_t)batch * plan.cells : nullptr;
     w.hist = c.take<uint32_t>((size_t)batch * plan.K * plan.cells);
     w.vid = c.take<int32_t>((size_t)batch * plan.cells);
     w.cutoff = c.take<int32_t>((size_t)batch);
@@ -493,7 +538,7 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
         const float m = frexpf(a.vs[j], &e);
         a.inv[j] = (m == 0.5f && e > -100 && e < 100) ? 1.0f / a.vs[j] : 0.0f;
     }
-    a.cells = plan.cells; a.K = plan.K; a.T = plan.T;
+    a.cells = plan.cells; a.K = plan.K; a.T = plan.T; a.G = plan.G;
     a.apply_shift = p->apply_z_shift; a.z_shift = p->z_shift;
     a.max_points = p->max_points; a.max_voxels = p->max_voxels; a.reverse = p->reverse_index;
     a.ws = ws; a.coors = coors; a.num_points = num_points; a.voxel_count = voxel_count;
@@ -501,7 +546,7 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
 
     GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     GND_CUDA_CHECK(cudaFuncSetAttribute(vox_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
-    GND_CUDA_CHECK(cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * plan.cells * sizeof(int32_t), stream));
+    GND_CUDA_CHECK(cudaMemsetAsync(ws.first, 0x7f, ((size_t)batch * plan.cells + (size_t)batch) * sizeof(int32_t), stream));
     if (n_points > 0) {
         if (plan.tiled) {
             GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -514,7 +559,7 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     } else {
         GND_CUDA_CHECK(cudaMemsetAsync(ws.hist, 0, (size_t)batch * plan.K * plan.cells * sizeof(uint32_t), stream));
     }
-    vox_assign_kernel<<<batch, 1024, plan.assign_smem, stream>>>(a);
+    vox_assign_kernel<<<batch * plan.G, 1024, plan.assign_smem, stream>>>(a);
     GND_LAUNCH_CHECK("vox_assign_kernel");
     if (n_points > 0) {
         int gx = (plan.T + 255) / 256;

@@ -18,6 +18,7 @@ struct VoxPlan {
     int32_t cells;       // nx*ny*nz
     int32_t K;           // chunks per scan
     int32_t T;           // points per chunk (multiple of VOX_SUB)
+    int32_t G;           // vox_assign_kernel CTAs per scan
     int32_t tiled;       // 1: vox_rank_tiles_kernel (grids <= VOX_RT_MAX_CELLS cells), 0: vox_rank_kernel
     size_t rank_smem;    // dynamic smem of the rank kernel
     size_t assign_smem;  // dynamic smem of the assign kernel
@@ -28,6 +29,7 @@ struct VoxWs {
     int32_t *cell;       // [B][N]      linear cell of every point, -1 if rejected
     uint16_t *lrank;     // [B][N]      rank of the point among its cell's points inside its chunk
     int32_t *first;      // [B][cells]  index of the first point of the cell (INT_MAX-like if none)
+    int32_t *done;       // [B]         assign CTAs finished per scan (counts up from the 0x7f fill, self-resetting)
     uint32_t *hist;      // [B][K][cells] chunk histogram -> exclusive prefix over chunks (in place)
     int32_t *vid;        // [B][cells]  voxel id of the cell, -1 if none
     int32_t *cutoff;     // [B]         first dropped index when max_voxels overflows, else INT_MAX
