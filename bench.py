@@ -44,6 +44,17 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
+def conv_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of the conv kernel, per launch, from the committed ncu --set full
+    capture of this workload (profiles/conv_traffic.json, written by tools/make_profile_summary.py)."""
+    p = os.path.join(ROOT, "profiles", "conv_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    with open(p) as f:
+        d = json.load(f)
+    return d["bytes_per_launch"], d["source"]
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -90,7 +101,7 @@ class ClockSampler:
 
 
 def make_scans(seeds):
-    from oracle import synth
+    from gndnet_b200 import synth
     return np.stack([synth.hdl64_scan(int(s)) for s in seeds]).astype(np.float32)
 
 
@@ -133,6 +144,57 @@ def cpu_baseline(seconds, warm=2, pool=16):
             "sample": "%d synthetic HDL-64 scans of %d points, batch 1, %.1f s of CPU work (voxelize %.0f%% / torch-CPU "
                       "forward %.0f%% / segment %.0f%%); checkpoint %s" % (n_scans, N_POINTS, total, 100 * parts[0] / total,
                                                                            100 * parts[1] / total, 100 * parts[2] / total, ck)}, total
+
+
+def torch_cuda_baseline(seconds=3.0):
+    """The reference's GPU deployment shape (ros_node.py:61-66, 96-126) as a side baseline: CPU voxelization ->
+    pageable H2D of the dense [M,100,4] voxels -> eager PyTorch CUDA forward (cuDNN, torch's default TF32 policy)
+    -> D2H of the map -> CPU segment_cloud, one scan at a time; plus the forward alone on resident tensors."""
+    import torch
+    from oracle import cpu_ops, model_ref, synth
+    cfg = synth.make_cfg("kitti")
+    sd, ck = synth.checkpoint("kitti")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    with model_ref.on_device(dev):
+        sd_dev = {k: model_ref._t(v) for k, v in sd.items()}
+        scans = [synth.hdl64_scan(9100 + i) for i in range(8)]
+
+        def one(raw, fwd_only=None):
+            pts = raw.copy()
+            cpu_ops.shift_cloud(pts, cfg.lidar_height)
+            v, c, n = cpu_ops.points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+            c4 = np.concatenate([np.zeros((len(c), 1), np.float32), c.astype(np.float32)], 1)
+            with torch.no_grad():
+                vt, ct, nt = (torch.from_numpy(x).to(dev) for x in (v, c4, n.astype(np.float32)))
+                if fwd_only is not None:
+                    return vt, ct, nt
+                h = model_ref.forward(sd_dev, cfg, vt, ct, nt).cpu().numpy()
+            cpu_ops.segment_cloud(pts.copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0], h.T, 0.08)
+
+        for s_ in scans[:3]:
+            one(s_)
+        torch.cuda.synchronize()
+        t0, k = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds:
+            one(scans[k % 8]); k += 1
+        torch.cuda.synchronize()
+        e2e = k / (time.perf_counter() - t0)
+        vt, ct, nt = one(scans[0], fwd_only=True)
+        with torch.no_grad():
+            for _ in range(5):
+                model_ref.forward(sd_dev, cfg, vt, ct, nt)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(50):
+                model_ref.forward(sd_dev, cfg, vt, ct, nt)
+            b.record()
+            torch.cuda.synchronize()
+        fwd_ms = a.elapsed_time(b) / 50
+    return {"value": e2e, "unit": "scans/s", "kind": "port",
+            "what": "ros_node.py shape, batch 1: C voxelizer (numba port) on the host -> pageable H2D of dense voxels -> eager "
+                    "torch CUDA forward (cuDNN, allow_tf32=%s) -> D2H map -> C segment_cloud; %d scans in %.1f s" %
+                    (torch.backends.cudnn.allow_tf32, k, seconds),
+            "forward_only_ms_batch1": fwd_ms, "checkpoint": ck}
 
 
 def run_reference(args, rank):
@@ -192,7 +254,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from oracle import synth
+    from gndnet_b200 import synth
     from gndnet_b200.model import GroundEstimatorNet
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: there is no CPU fallback"
     torch.cuda.set_device(local)
@@ -319,12 +381,38 @@ def main():
         conv_ms = st["segnet_convs"]
         achieved = GFLOP_PER_SCAN * (1 - 0.0115 / GFLOP_PER_SCAN) * B / conv_ms     # TFLOP/s (GFLOP / ms)
         peak = pk["tf_sust"]
+        issued = sum(g * (3.0 if (args.precision == "split" or (args.precision == "mixed" and i < 4)) else 1.0)
+                     for i, g in enumerate(CONV_GFLOP)) * B / conv_ms if args.precision != "fp32" else achieved
+        traffic, traffic_src = conv_traffic()
         extra["roofline"] = {"bound": "tensor", "kernel": st["conv_kernel"], "achieved": achieved, "peak": peak,
-                             "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                             "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)",
+                             "traffic_source": traffic_src,
                              "peak_source": pk["src"] + " sustained bf16 (kernel timed inside a long step)",
-                             "launch_ms_avg": conv_ms / 8.0}
+                             "launch_ms_avg": conv_ms / 8.0,
+                             "issued_tflops": issued, "issued_frac": issued / peak,
+                             "issued_note": "MMA work actually issued: the four encoder layers run three fp16 products per "
+                                            "algorithmic product (split-fp16, DESIGN.md 3)"}
+        # the HBM-bound stages: algorithmic bytes (SURVEY.md 8d / DESIGN.md 5) over the measured stage time
+        pil = model.pillars(B)
+        M = pil["voxel_count"].long()
+        S = int(torch.gather(pil["point_offsets"].long(), 1, M.view(-1, 1)).sum().item())
+        Msum = int(M.sum().item())
+        e_canvas = 4 if args.precision == "fp32" else 4          # fp32 plane, or fp16 hi + lo planes
+        alg = {"voxelize": B * N_POINTS * 16 + 16 * Msum + 4 * S,
+               "pfn_scatter": 16 * S + 16 * Msum + B * 64 * model.ny * model.nx * e_canvas,
+               "segment": B * (N_POINTS * 12 + model.ny * model.nx * 4 + N_POINTS)}
+        extra["hbm_stages"] = {k: {"algorithmic_mb": alg[k] / 1e6, "ms": st[k], "achieved_gbs": alg[k] / 1e6 / st[k],
+                                   "frac_of_measured_hbm": alg[k] / 1e6 / st[k] / pk["hbm"],
+                                   "frac_of_nominal_8tbs": alg[k] / 1e6 / st[k] / 8000.0} for k in alg}
+        extra["hbm_stages"]["pillars_per_scan"] = Msum / B
+        extra["hbm_stages"]["kept_points_per_scan"] = S / B
+        extra["hbm_stages"]["peak_gbs"] = pk["hbm"]
         if not args.no_cpu_baseline:
             extra["cpu_baseline"], _ = cpu_baseline(args.cpu_seconds)
+            try:
+                extra["torch_cuda_baseline"] = torch_cuda_baseline()
+            except Exception as ex:        # a side baseline must never take the bench line down
+                extra["torch_cuda_baseline"] = {"unavailable": repr(ex)[:200]}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "scans/s", "n_gpus": world, "steps": args.steps,

@@ -19,10 +19,29 @@ BN2D_EPS = 1e-5   # nn.BatchNorm2d default, modules/segnet.py:35-38
 BN1D_EPS = 1e-3   # modules/pointpillars.py:42
 
 
+_DEV = torch.device("cpu")     # the oracle runs on the CPU; bench.py's torch-CUDA side baseline sets "cuda"
+
+
+class on_device:
+    """with on_device("cuda"): the same eager torch ops on the GPU (cuDNN convolutions) -- the reference's
+    PyTorch CUDA forward (ros_node.py:61-66, 211) as a timed side baseline, never a checker."""
+
+    def __init__(self, dev):
+        self.dev = torch.device(dev)
+
+    def __enter__(self):
+        global _DEV
+        self.prev, _DEV = _DEV, self.dev
+
+    def __exit__(self, *exc):
+        global _DEV
+        _DEV = self.prev
+
+
 def _t(x):
     if isinstance(x, torch.Tensor):
-        return x.detach().to(torch.float32).cpu()
-    return torch.from_numpy(np.ascontiguousarray(x)).to(torch.float32)
+        return x.detach().to(_DEV, torch.float32)
+    return torch.from_numpy(np.ascontiguousarray(x)).to(_DEV, torch.float32)
 
 
 def grid_shape(cfg):
@@ -51,7 +70,7 @@ def pillar_feature_net(sd, cfg, voxels, num_points, coors):
         ls.append(torch.norm(features[:, :, :3], 2, 2, keepdim=True))                        # :130-132
     features = torch.cat(ls, dim=-1)
     P = features.shape[1]
-    mask = (num_voxels.int().unsqueeze(1) > torch.arange(P, dtype=torch.int).view(1, -1))    # :202-223
+    mask = (num_voxels.int().unsqueeze(1) > torch.arange(P, dtype=torch.int, device=_DEV).view(1, -1))    # :202-223
     features = features * mask.unsqueeze(-1).to(features.dtype)                              # :137-140
     pre = "voxel_feature_extractor.pfn_layers.0."
     w = _t(sd[pre + "linear.weight"])
@@ -74,7 +93,7 @@ def pillars_scatter(cfg, voxel_features, coors, batch_size):
     C = voxel_features.shape[1]
     out = []
     for b in range(batch_size):
-        canvas = torch.zeros(C, nx * ny, dtype=voxel_features.dtype)
+        canvas = torch.zeros(C, nx * ny, dtype=voxel_features.dtype, device=voxel_features.device)
         m = coors[:, 0] == b
         tc = coors[m, :]
         idx = (tc[:, 2] * nx + tc[:, 3]).long()

@@ -7,7 +7,7 @@ import numpy as np
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from oracle import synth  # noqa: E402
+from gndnet_b200 import synth  # noqa: E402
 from gndnet_b200.model import GroundEstimatorNet  # noqa: E402
 
 ap = argparse.ArgumentParser()
