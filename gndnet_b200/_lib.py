@@ -42,6 +42,11 @@ class Config(ctypes.Structure):
                 ("use_norm", c_i32), ("with_distance", c_i32), ("precision", c_i32)]
 
 
+class UnpackParams(ctypes.Structure):
+    _fields_ = [("point_step", c_i32), ("has_transform", c_i32), ("transform", c_d * 16), ("drop_nan", c_i32),
+                ("out_features", c_i32)]
+
+
 class Weight(ctypes.Structure):
     _fields_ = [("name", ctypes.c_char_p), ("h_data", ctypes.POINTER(c_f)), ("numel", c_i64)]
 
@@ -71,6 +76,9 @@ _SIGS = {
     "gnd_segnet_profile": (ctypes.c_int, [c_vp, c_i32, c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_f), c_vp]),
     "gnd_segment": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_vp, c_d, c_vp, c_vp, c_vp]),
     "gnd_infer": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_d, c_vp, c_vp, c_vp, c_vp]),
+    "gnd_unpack_workspace_bytes": (ctypes.c_int, [c_i64, ctypes.POINTER(c_sz)]),
+    "gnd_unpack_cloud": (ctypes.c_int, [ctypes.POINTER(UnpackParams), c_vp, c_i64, c_vp, c_sz, c_vp, c_vp, c_vp]),
+    "gnd_pack_segmented": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "gnd_get_buffer": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),
     "gnd_last_launch_count": (ctypes.c_int, [c_vp]),
 }

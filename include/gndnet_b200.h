@@ -200,6 +200,39 @@ GND_API int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *counts, 
                       int64_t n_points, double threshold, float *height, int8_t *labels_i8,
                       double *labels_f64, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Streaming-node I/O either side of the path.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct gnd_unpack_params {
+    int32_t point_step;      /* msg.point_step: x, y, z float32 at byte offsets 0, 4, 8 of each row
+                                (utils/utils.py:179-180)                                        */
+    int32_t has_transform;   /* 1: apply `transform` (utils/transform.py:148-165 transformCloud) */
+    double transform[16];    /* row-major 4x4 (transform.py:107-111, :99-105), float64           */
+    int32_t drop_nan;        /* 1: drop rows with a NaN after the transform (ros_node.py:263)    */
+    int32_t out_features;    /* columns of the output rows, >= 3 (extra columns are zero)        */
+} gnd_unpack_params;
+
+GND_API int gnd_unpack_workspace_bytes(int64_t n_points, size_t *h_bytes);
+/*
+ * Replaces ros_node.py:242-263: cloud_msg_to_numpy(msg)["xyz"] (utils/utils.py:148-195), transformCloud
+ * (utils/transform.py:148-165) and the NaN filter, on the device.
+ * msg_data   [n_points][point_step] bytes of sensor_msgs/PointCloud2.data (device)
+ * out_points [n_points][out_features] float32; the first *out_count rows are valid, input order kept
+ * out_count  device int32 -- usable directly as gnd_infer's `counts`
+ */
+GND_API int gnd_unpack_cloud(const gnd_unpack_params *p, const uint8_t *msg_data, int64_t n_points,
+                             void *workspace, size_t workspace_bytes, float *out_points,
+                             int32_t *out_count, void *stream);
+/*
+ * Replaces utils/ros_utils.py:171-191 np2ros_pub_2 up to the msgify call: the 16-byte wire rows
+ * (x, y, z, intensity = label as float32) of the segmented cloud.  One of labels_i8 / labels_f64.
+ * (utils/ros_utils.py:210-248 array_to_pointcloud2's 12-byte rows are what gnd_compact_obstacles
+ * writes for obstacle_features == 3.)
+ */
+GND_API int gnd_pack_segmented(const float *points, int64_t n_points, int32_t num_features,
+                               const int8_t *labels_i8, const double *labels_f64, float *out_rows,
+                               void *stream);
+
 /* Test / profiling hook: device pointer + bytes of a named workspace buffer ("canvas", "coors",
  * "num_points", "voxel_count", "point_offsets", "point_list", "act:<stage>", ...). */
 GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *bytes);

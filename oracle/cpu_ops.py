@@ -52,6 +52,11 @@ def lib():
             c_fp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64,
             ctypes.c_double, c_dp, c_fp, ctypes.c_int]
         L.gnd_oracle_segment_cloud.restype = ctypes.c_int64
+        L.gnd_oracle_unpack_cloud.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, c_dp, ctypes.c_int,
+                                              ctypes.c_int, c_fp]
+        L.gnd_oracle_unpack_cloud.restype = ctypes.c_int64
+        L.gnd_oracle_pack_segmented.argtypes = [c_fp, ctypes.c_int64, ctypes.c_int, c_dp, c_fp]
+        L.gnd_oracle_pack_segmented.restype = None
         _lib = L
     return _lib
 
@@ -134,3 +139,25 @@ def segment_cloud_noground(points, points_obstacle, grid_size, voxel_size, eleva
                            threshold=0.2):
     labels, cnt = _segment(points, points_obstacle, grid_size, voxel_size, elevation_map, threshold)
     return labels, points_obstacle[:cnt]
+
+
+def unpack_cloud(data, point_step, trafo=None, drop_nan=True, out_cols=3):
+    """ros_node.py:242-263 up to the NaN filter: msg.data bytes -> xyz rows (utils/utils.py:179-180), optional
+    transformCloud with a 4x4 float64 matrix (utils/transform.py:148-165), NaN rows dropped in order."""
+    buf = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.view(np.uint8).reshape(-1))
+    n = buf.size // point_step
+    out = np.zeros((n, out_cols), dtype=np.float32)
+    t = None if trafo is None else np.ascontiguousarray(np.asarray(trafo, dtype=np.float64).reshape(16))
+    tp = t.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if t is not None else None
+    m = lib().gnd_oracle_unpack_cloud(buf.ctypes.data, n, point_step, tp, 1 if drop_nan else 0, out_cols, _fp(out))
+    return out[:m]
+
+
+def pack_segmented(points, labels):
+    """utils/ros_utils.py:171-191 np2ros_pub_2: the 16-byte (x, y, z, intensity=label) wire rows, as bytes."""
+    points = np.ascontiguousarray(points, dtype=np.float32)
+    lab = np.ascontiguousarray(labels, dtype=np.float64)
+    out = np.empty((points.shape[0], 4), dtype=np.float32)
+    lib().gnd_oracle_pack_segmented(_fp(points), points.shape[0], points.shape[1],
+                                    lab.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), _fp(out))
+    return out

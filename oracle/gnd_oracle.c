@@ -177,3 +177,52 @@ GND_EXPORT int64_t gnd_oracle_segment_cloud(
     }
     return obs_cnt;
 }
+
+/* ---------------------------------------------------------------------------
+ * SURVEY.md 8(f) row 1 -- the steps immediately upstream of the voxelizer in the streaming node:
+ *   utils/utils.py:148-195  cloud_msg_to_numpy: xyz = the first 12 bytes of every point_step-byte row of
+ *                           msg.data viewed as three little-endian float32 (:179-180)
+ *   utils/transform.py:148-165 transformCloud: v = append(xyz, 1.0) (float64), res = dot(trafo, v) (float64,
+ *                           numba np.dot on a 4x4 @ 4 -> row sums in k order), points[i] = res[:3] as float32
+ *   ros_node.py:263         cloud = cloud[~np.isnan(cloud).any(axis=1)]  (stable, after the transform)
+ * out is [n][out_cols] float32 (out_cols >= 3, extra columns zero); returns the number of rows kept.
+ * ------------------------------------------------------------------------- */
+GND_EXPORT int64_t gnd_oracle_unpack_cloud(const uint8_t *data, int64_t n, int32_t point_step, const double *trafo,
+                                           int drop_nan, int out_cols, float *out)
+{
+    int64_t m = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        float p[3];
+        memcpy(p, data + i * (int64_t)point_step, 12);
+        if (trafo) {
+            const double v[4] = {(double)p[0], (double)p[1], (double)p[2], 1.0};
+            for (int r = 0; r < 3; ++r) {
+                volatile double acc = 0.0;
+                for (int k = 0; k < 4; ++k) acc = acc + trafo[4 * r + k] * v[k];
+                p[r] = (float)acc;
+            }
+        }
+        if (drop_nan && (isnan(p[0]) || isnan(p[1]) || isnan(p[2]))) continue;
+        float *o = out + m * out_cols;
+        o[0] = p[0]; o[1] = p[1]; o[2] = p[2];
+        for (int j = 3; j < out_cols; ++j) o[j] = 0.0f;
+        ++m;
+    }
+    return m;
+}
+
+/* SURVEY.md 8(f) row 2 -- the wire layouts immediately downstream:
+ *   utils/ros_utils.py:171-191 np2ros_pub_2: structured rows (x, y, z, intensity) float32, 16 bytes per point,
+ *                           intensity = the segment_cloud label (float64 -> float32)
+ *   utils/ros_utils.py:210-248 array_to_pointcloud2 without colours: 12-byte rows x, y, z (the compacted obstacle
+ *                           rows of segment_cloud_noground are already in this layout)
+ * points is [n][cols] float32; out is [n][4] float32. */
+GND_EXPORT void gnd_oracle_pack_segmented(const float *points, int64_t n, int cols, const double *labels, float *out)
+{
+    for (int64_t i = 0; i < n; ++i) {
+        out[4 * i + 0] = points[i * cols + 0];
+        out[4 * i + 1] = points[i * cols + 1];
+        out[4 * i + 2] = points[i * cols + 2];
+        out[4 * i + 3] = (float)labels[i];
+    }
+}

@@ -1,0 +1,90 @@
+"""GPU parity for the steps either side of the hot path, through the C ABI:
+message bytes -> xyz -> float64 rigid transform -> NaN filter upstream; wire-row packing downstream.
+Bit-exact against the reference's goldens and against the C oracle on seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_ops, synth
+from tests import cases, helpers
+from gndnet_b200 import ros_io
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", ["step16", "step18_unaligned", "step12_identity", "empty", "all_nan"])
+def test_unpack_matches_reference_golden(name, cuda):
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        raw, trafo, want = z[name + "__msg"], z[name + "__trafo"], z[name + "__cloud"]
+    t = trafo.reshape(4, 4) if trafo.size else None
+    pts, cnt = ros_io.unpack_cloud(raw, raw.shape[1], t, True, 3)
+    m = int(cnt.item())
+    assert m == len(want)
+    assert pts[:m].cpu().numpy().tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("n,step,feat,drop", [(120000, 32, 4, True), (1000003, 16, 3, True), (50000, 22, 3, False),
+                                              (1, 12, 3, True), (1025, 20, 4, True)])
+def test_unpack_matches_oracle(n, step, feat, drop, cuda):
+    rng = np.random.default_rng(n + step)
+    raw = rng.integers(0, 256, size=(n, step), dtype=np.uint8)
+    xyz = (rng.random((n, 3)) * 200 - 100).astype(np.float32)
+    xyz[rng.random(n) < 0.05, 1] = np.nan
+    xyz[rng.random(n) < 0.01, 2] = -np.inf
+    raw[:, :12] = xyz.view(np.uint8).reshape(n, 12)
+    ts = synth.SimpleNamespace(transform=synth.SimpleNamespace(
+        translation=synth.SimpleNamespace(x=0.3, y=-2.5, z=1.733),
+        rotation=synth.SimpleNamespace(x=0.0616284, y=0.0616284, z=0.7044160, w=0.7044160)))
+    trafo = ros_io.transformStampedToTransformationMatrix(ts)
+    want = cpu_ops.unpack_cloud(raw, step, trafo, drop, feat)
+    pts, cnt = ros_io.unpack_cloud(torch.from_numpy(raw).cuda(), step, trafo, drop, feat)
+    m = int(cnt.item())
+    assert m == len(want)
+    got = pts[:m].cpu().numpy()
+    # NaN payload bits are not part of the contract when rows are kept (drop=False): compare values
+    assert np.array_equal(got, want, equal_nan=True)
+    if drop:
+        assert got.tobytes() == want.tobytes()
+
+
+def test_pack_segmented_and_obstacle_rows(cuda):
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        pts, lab, wire = z["pack__points"], z["pack__labels"], z["pack__wire16"]
+    p = torch.from_numpy(pts).cuda()
+    for l in (torch.from_numpy(lab).cuda(), torch.from_numpy(lab.astype(np.int8)).cuda()):
+        rows = ros_io.pack_segmented(p, l)
+        assert rows.cpu().numpy().tobytes() == wire.tobytes()
+    obs, cnt = ros_io.obstacle_rows(p, torch.from_numpy(lab.astype(np.int8)).cuda())
+    m = int(cnt.item())
+    assert obs[:m].cpu().numpy().tobytes() == np.ascontiguousarray(pts[lab == 1]).tobytes()   # array_to_pointcloud2 rows
+
+
+def test_message_to_labels_chain(cuda):
+    """ros_node.py:242-288 end to end on the device: message bytes -> cloud (ragged count stays on the GPU) ->
+    infer -> labels -> wire rows, against the same chain on the oracle."""
+    cfg = synth.make_cfg("kitti", batch_size=1)
+    model, sd = helpers.load_model(cfg, "kitti", "fp32", cuda)
+    scan = synth.hdl64_scan(321)[::3].copy()
+    n = len(scan)
+    rng = np.random.default_rng(5)
+    raw = rng.integers(0, 256, size=(n, 16), dtype=np.uint8)
+    xyz = scan[:, :3].copy()
+    xyz[rng.random(n) < 0.02, 0] = np.nan
+    raw[:, :12] = xyz.view(np.uint8).reshape(n, 12)
+    c, s = np.cos(0.1), np.sin(0.1)
+    trafo = np.array([[c, -s, 0, 0.5], [s, c, 0, -0.25], [0, 0, 1, 0.0], [0, 0, 0, 1]], dtype=np.float64)
+    want_cloud = cpu_ops.unpack_cloud(raw, 16, trafo, True, 4)
+    pts, cnt = ros_io.unpack_cloud(raw, 16, trafo, True, 4)
+    with torch.no_grad():
+        height, lab = model.infer(pts.unsqueeze(0), threshold=0.16, counts=cnt, labels="int8")
+    m = int(cnt.item())
+    assert m == len(want_cloud)
+    # oracle chain on the kept rows
+    ref_pts = want_cloud.copy()
+    cpu_ops.shift_cloud(ref_pts, cfg.lidar_height)
+    exp = cpu_ops.segment_cloud(ref_pts.copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0],
+                                height[0].cpu().numpy().T, 0.16)
+    got = lab[0, :m].cpu().numpy().astype(np.float64)
+    assert np.array_equal(got, exp)
+    rows = ros_io.pack_segmented(pts[:m].contiguous(), lab[0, :m].contiguous())
+    assert rows.cpu().numpy().tobytes() == cpu_ops.pack_segmented(want_cloud, exp).tobytes()

@@ -62,3 +62,23 @@ def test_model_restatement_matches_reference_heights():
                 cs.append(np.concatenate([np.full((len(c), 1), b, np.float32), c.astype(np.float32)], 1))
             out = model_ref.forward(sd, cfg, np.concatenate(vs), np.concatenate(cs), np.concatenate(ns)).numpy()
             assert np.abs(out - z[key]).max() <= 2e-5
+
+
+IO_CASES = ["step16", "step18_unaligned", "step12_identity", "empty", "all_nan"]
+
+
+@pytest.mark.parametrize("name", IO_CASES)
+def test_cloud_unpack_matches_reference_golden(name):
+    """msg bytes -> xyz -> transformCloud -> NaN filter, against the clouds the unmodified
+    reference produced in the build container (oracle/ref_harness_io.py)."""
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        raw, trafo, want = z[name + "__msg"], z[name + "__trafo"], z[name + "__cloud"]
+    got = cpu_ops.unpack_cloud(raw, raw.shape[1], trafo.reshape(4, 4) if trafo.size else None, True, 3)
+    assert got.shape == want.shape and got.tobytes() == want.tobytes()
+
+
+def test_pack_segmented_matches_reference_golden():
+    """np2ros_pub_2's 16-byte wire rows."""
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        pts, lab, wire = z["pack__points"], z["pack__labels"], z["pack__wire16"]
+    assert cpu_ops.pack_segmented(pts, lab).tobytes() == wire.tobytes()
