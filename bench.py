@@ -270,7 +270,10 @@ def main():
     model = model.to(dev).eval()
     B = args.batch
     # two distinct batches per rank, rotated every step: 2 x 123 MB of inputs > 126 MB L2
-    seeds = 100000 * (rank + 1) + np.arange(2 * B)
+    # the global batch of world * B scans is sharded by scan: rank r owns [lo, hi) (gndnet_b200.pipeline.shard_range)
+    from gndnet_b200.pipeline import shard_range, max_over_ranks
+    lo, hi = shard_range(world * B, rank, world)
+    seeds = 100000 + np.concatenate([np.arange(lo, hi), world * B + np.arange(lo, hi)])
     host = make_scans(seeds).reshape(2, B, N_POINTS, 4)
     pinned = [torch.from_numpy(host[i]).pin_memory() for i in range(2)]
     resident = [p.to(dev) for p in pinned]
@@ -311,10 +314,8 @@ def main():
             clocks = sampler.stop() if sampler else None
             ms = e0.elapsed_time(e1)
             if world > 1:
-                t = torch.tensor([ms], device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = max_over_ranks(ms, device=dev)
                 dist.barrier()
-                ms = float(t.item())
         return ms, clocks
 
     ms, clocks = timed(step_resident, args.steps, args.warmup, sample_clocks=(rank == 0))

@@ -110,3 +110,38 @@ class GraphedInfer:
             self.points.copy_(points.reshape(self.points.shape), non_blocking=True)
         self.graph.replay()
         return self.height, self.labels
+
+
+# ---------------------------------------------------------------------------------------- multi-GPU plumbing
+# The path shards by scan with no exchange step: one process per GPU, rank r owns the scans
+# shard_range(n, r, world) and a full weight replica.  The only collectives are the barrier and the MAX of the
+# timed milliseconds in bench.py, and the optional gather of per-rank result counts below.
+
+def shard_range(n_items, rank, world):
+    """Contiguous balanced split: rank r gets items [lo, hi); sizes differ by at most one, earlier ranks larger."""
+    if world < 1 or not (0 <= rank < world) or n_items < 0:
+        raise ValueError("bad shard request: n=%d rank=%d world=%d" % (n_items, rank, world))
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def max_over_ranks(value, device=None):
+    """MAX of a per-rank scalar (the timed milliseconds) over the default process group; identity without one."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device if device is not None else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def gather_shard_sizes(n_local, device=None):
+    """Every rank's item count (e.g. scans processed), as a list indexed by rank."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [int(n_local)]
+    t = torch.tensor([int(n_local)], dtype=torch.int64, device=device if device is not None else "cpu")
+    out = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [int(x.item()) for x in out]
