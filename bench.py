@@ -105,6 +105,18 @@ def make_scans(seeds):
     return np.stack([synth.hdl64_scan(int(s)) for s in seeds]).astype(np.float32)
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core it can."""
+    import torch
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def cpu_path_scan(sd, cfg, raw):
     """The reference's CPU path on the oracle port: numba loop -> C restatement, torch CPU forward, segment."""
     import torch
@@ -128,6 +140,7 @@ def cpu_baseline(seconds, warm=2, pool=16):
     of CPU work have been timed."""
     import torch
     from oracle import synth
+    use_all_host_threads()
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
     scans = [synth.hdl64_scan(9000 + i) for i in range(pool)]
@@ -204,6 +217,7 @@ def run_reference(args, rank):
             "points_per_scan": N_POINTS, "batch_per_gpu": args.batch,
             "sample_per_step": "%d scans of the batch (bounded sample), one at a time like predict_ground.py" % args.ref_scans_per_step}
     from oracle import synth
+    use_all_host_threads()
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
     per = args.ref_scans_per_step
@@ -408,7 +422,7 @@ def main():
         extra["hbm_stages"]["pillars_per_scan"] = Msum / B
         extra["hbm_stages"]["kept_points_per_scan"] = S / B
         extra["hbm_stages"]["peak_gbs"] = pk["hbm"]
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:
             extra["cpu_baseline"], _ = cpu_baseline(args.cpu_seconds)
             try:
                 extra["torch_cuda_baseline"] = torch_cuda_baseline()
