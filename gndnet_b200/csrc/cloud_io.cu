@@ -176,3 +176,96 @@ extern "C" int gnd_pack_segmented(const float *points, int64_t n_points, int32_t
     GND_LAUNCH_CHECK("pack_segmented_kernel");
     return GND_OK;
 }
+
+// ---- the evaluation reductions of evaluate_SemanticKITTI.py on the device ----------------
+//   :94-100  get_GndSeg: 0 for the ground classes, -1 for sem_label in {0, 1} (unlabelled / outlier), else 1
+//   :102-111 remove_outliers: keep points with pred >= 0 and GndSeg >= 0, then ground = 1 - value
+//   :198-204 intersection / union / pred sum / GT sum over the kept points (integers: exact, order-free)
+//   :224-226 mse = sum(square(target - pred.T) * mask) / sum(mask) in float64
+namespace gnd {
+
+struct EvalArgs {
+    const int8_t *lab8;
+    const double *lab64;
+    const uint32_t *sem;
+    int64_t n;
+    int32_t n_classes;
+    uint32_t classes[16];
+    unsigned long long *counts;      // [4]: intersection, union, predicted ground, GT ground
+};
+
+__global__ void __launch_bounds__(256) eval_counts_kernel(const EvalArgs a) {
+    unsigned c_i = 0, c_u = 0, c_p = 0, c_g = 0;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * 256) {
+        const int pred = a.lab8 ? (int)a.lab8[i] : (int)a.lab64[i];
+        const uint32_t s = __ldg(a.sem + i);
+        bool is_gnd = false;
+        for (int k = 0; k < a.n_classes; ++k) is_gnd |= (s == a.classes[k]);
+        const int gt = (s == 0u || s == 1u) ? -1 : (is_gnd ? 0 : 1);       // the {0,1} assignment comes second (:98-99)
+        if (pred >= 0 && gt >= 0) {
+            const bool pg = pred == 0, gg = gt == 0;
+            c_i += (pg && gg); c_u += (pg || gg); c_p += pg; c_g += gg;
+        }
+    }
+    c_i = __reduce_add_sync(0xffffffffu, c_i); c_u = __reduce_add_sync(0xffffffffu, c_u);
+    c_p = __reduce_add_sync(0xffffffffu, c_p); c_g = __reduce_add_sync(0xffffffffu, c_g);
+    if ((threadIdx.x & 31) == 0) {
+        if (c_i) atomicAdd(a.counts + 0, (unsigned long long)c_i);
+        if (c_u) atomicAdd(a.counts + 1, (unsigned long long)c_u);
+        if (c_p) atomicAdd(a.counts + 2, (unsigned long long)c_p);
+        if (c_g) atomicAdd(a.counts + 3, (unsigned long long)c_g);
+    }
+}
+
+// one block, fixed reduction tree: the float64 sums are reproducible run to run
+__global__ void __launch_bounds__(1024) eval_sqerr_kernel(const float *pred, const double *target, const double *mask,
+                                                          int nx, int ny, double *sums) {
+    __shared__ double s_a[1024], s_b[1024];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < nx * ny; i += 1024) {
+        const int x = i / ny, y = i - x * ny;                 // target / mask are [nx][ny]; pred.T[x][y] = pred[y][x]
+        const double d = target[i] - (double)pred[(size_t)y * nx + x];
+        a += d * d * mask[i];
+        b += mask[i];
+    }
+    s_a[threadIdx.x] = a; s_b[threadIdx.x] = b;
+    __syncthreads();
+    for (int s = 512; s > 0; s >>= 1) {
+        if (threadIdx.x < s) { s_a[threadIdx.x] += s_a[threadIdx.x + s]; s_b[threadIdx.x] += s_b[threadIdx.x + s]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { sums[0] = s_a[0]; sums[1] = s_b[0]; }
+}
+
+}  // namespace gnd
+
+extern "C" int gnd_eval_ground_counts(const int8_t *labels_i8, const double *labels_f64, const uint32_t *sem_label,
+                                      int64_t n_points, const uint32_t *h_ground_classes, int32_t n_classes,
+                                      uint64_t *counts4, void *stream) {
+    g_launches = 0;
+    if (n_points < 0 || n_classes < 0 || n_classes > 16) return fail(GND_ERR_INVALID, "bad n_points / n_classes (<= 16)");
+    if (!counts4 || (n_classes && !h_ground_classes)) return fail(GND_ERR_INVALID, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    GND_CUDA_CHECK(cudaMemsetAsync(counts4, 0, 4 * sizeof(uint64_t), st));
+    if (n_points == 0) return GND_OK;
+    if ((!labels_i8 && !labels_f64) || !sem_label) return fail(GND_ERR_INVALID, "null pointer");
+    EvalArgs a;
+    a.lab8 = labels_i8; a.lab64 = labels_f64; a.sem = sem_label; a.n = n_points; a.n_classes = n_classes;
+    for (int k = 0; k < 16; ++k) a.classes[k] = k < n_classes ? h_ground_classes[k] : 0u;
+    a.counts = reinterpret_cast<unsigned long long *>(counts4);
+    int blocks = (int)((n_points + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    eval_counts_kernel<<<blocks, 256, 0, st>>>(a);
+    GND_LAUNCH_CHECK("eval_counts_kernel");
+    return GND_OK;
+}
+
+extern "C" int gnd_eval_masked_sqerr(const float *pred, const double *target, const double *mask, int32_t nx, int32_t ny,
+                                     double *sums2, void *stream) {
+    g_launches = 0;
+    if (nx < 1 || ny < 1) return fail(GND_ERR_INVALID, "empty map");
+    if (!pred || !target || !mask || !sums2) return fail(GND_ERR_INVALID, "null pointer");
+    eval_sqerr_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(pred, target, mask, nx, ny, sums2);
+    GND_LAUNCH_CHECK("eval_sqerr_kernel");
+    return GND_OK;
+}

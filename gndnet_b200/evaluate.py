@@ -1,0 +1,56 @@
+"""Device-side evaluation reductions of the reference's evaluate_SemanticKITTI.py.
+
+  ground_metrics(pred_labels, sem_label, GndClasses) -> (iou, prec, recall)
+        get_GndSeg (:94-100) + remove_outliers (:102-111) + the ratios of :198-204, from four exact integer counts
+  masked_mse(pred_gnd, target_gnd, gnd_mask) -> mse                                   :224-226
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+GND_CLASSES = (40, 44, 48, 49, 60, 72)        # evaluate_SemanticKITTI.py:190
+
+
+def ground_counts(pred_labels, sem_label, GndClasses=GND_CLASSES):
+    """int64 CUDA tensor [4]: intersection, union, predicted ground, GT ground (see include/gndnet_b200.h)."""
+    if not (pred_labels.is_cuda and pred_labels.dtype in (torch.int8, torch.float64) and pred_labels.is_contiguous()):
+        raise TypeError("pred_labels must be a contiguous int8 / float64 CUDA tensor")
+    if not (sem_label.is_cuda and sem_label.dtype in (torch.int32, torch.uint32) and sem_label.is_contiguous()
+            and sem_label.numel() == pred_labels.numel()):
+        raise TypeError("sem_label must be a contiguous 32-bit CUDA tensor with one entry per point")
+    cls = (ctypes.c_uint32 * len(GndClasses))(*[int(c) for c in GndClasses])
+    L = _lib.lib()
+    with torch.cuda.device(pred_labels.device):
+        out = torch.empty((4,), dtype=torch.int64, device=pred_labels.device)
+        l8 = pred_labels if pred_labels.dtype == torch.int8 else None
+        l64 = pred_labels if pred_labels.dtype == torch.float64 else None
+        _lib.check(L.gnd_eval_ground_counts(_lib.ptr(l8), _lib.ptr(l64), _lib.ptr(sem_label), pred_labels.numel(), cls,
+                                            len(GndClasses), _lib.ptr(out), _lib.stream_ptr()), "gnd_eval_ground_counts")
+    return out
+
+
+def ground_metrics(pred_labels, sem_label, GndClasses=GND_CLASSES):
+    """(iou, prec, recall) as the reference computes them (numpy float64 division of integer sums, :200-204)."""
+    c = ground_counts(pred_labels, sem_label, GndClasses).cpu().numpy()
+    with np.errstate(divide="ignore", invalid="ignore"):
+        return (np.float64(c[0]) / np.float64(c[1]), np.float64(c[0]) / np.float64(c[2]), np.float64(c[0]) / np.float64(c[3]))
+
+
+def masked_mse(pred_gnd, target_gnd, gnd_mask):
+    """pred_gnd [ny, nx] float32 CUDA (model output); target_gnd, gnd_mask [nx, ny] float64 CUDA -> python float."""
+    if not (pred_gnd.is_cuda and pred_gnd.dtype == torch.float32 and pred_gnd.dim() == 2 and pred_gnd.is_contiguous()):
+        raise TypeError("pred_gnd must be a contiguous float32 CUDA tensor [ny, nx]")
+    ny, nx = pred_gnd.shape
+    for t in (target_gnd, gnd_mask):
+        if not (t.is_cuda and t.dtype == torch.float64 and tuple(t.shape) == (nx, ny) and t.is_contiguous()):
+            raise TypeError("target_gnd / gnd_mask must be contiguous float64 CUDA tensors [nx, ny]")
+    L = _lib.lib()
+    with torch.cuda.device(pred_gnd.device):
+        sums = torch.empty((2,), dtype=torch.float64, device=pred_gnd.device)
+        _lib.check(L.gnd_eval_masked_sqerr(_lib.ptr(pred_gnd), _lib.ptr(target_gnd), _lib.ptr(gnd_mask), nx, ny,
+                                           _lib.ptr(sums), _lib.stream_ptr()), "gnd_eval_masked_sqerr")
+    s = sums.cpu().numpy()
+    return float(s[0] / s[1])

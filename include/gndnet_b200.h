@@ -233,6 +233,21 @@ GND_API int gnd_pack_segmented(const float *points, int64_t n_points, int32_t nu
                                const int8_t *labels_i8, const double *labels_f64, float *out_rows,
                                void *stream);
 
+/*
+ * Evaluation reductions.  Replaces evaluate_SemanticKITTI.py:94-111 (get_GndSeg,
+ * remove_outliers) and :198-204: counts4 (device uint64[4]) = intersection, union, predicted-ground and
+ * GT-ground counts over the points with pred >= 0 and a usable SemanticKITTI label; iou = c[0]/c[1],
+ * prec = c[0]/c[2], recall = c[0]/c[3].  h_ground_classes is a HOST list (<= 16) of ground class ids.
+ */
+GND_API int gnd_eval_ground_counts(const int8_t *labels_i8, const double *labels_f64,
+                                   const uint32_t *sem_label, int64_t n_points,
+                                   const uint32_t *h_ground_classes, int32_t n_classes,
+                                   uint64_t *counts4, void *stream);
+/* evaluate_SemanticKITTI.py:224-226: sums2 (device double[2]) = sum(square(target - pred.T) * mask), sum(mask).
+ * pred [ny][nx] float32 (the model output); target, mask [nx][ny] float64 (lidar_to_heightmap / lidar_to_img). */
+GND_API int gnd_eval_masked_sqerr(const float *pred, const double *target, const double *mask,
+                                  int32_t nx, int32_t ny, double *sums2, void *stream);
+
 /* Test / profiling hook: device pointer + bytes of a named workspace buffer ("canvas", "coors",
  * "num_points", "voxel_count", "point_offsets", "point_list", "act:<stage>", ...). */
 GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *bytes);

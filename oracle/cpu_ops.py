@@ -161,3 +161,23 @@ def pack_segmented(points, labels):
     lib().gnd_oracle_pack_segmented(_fp(points), points.shape[0], points.shape[1],
                                     lab.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), _fp(out))
     return out
+
+
+def ground_counts(pred_labels, sem_label, gnd_classes=(40, 44, 48, 49, 60, 72)):
+    """evaluate_SemanticKITTI.py:94-111, :198-204 restated with numpy (integer work): intersection, union,
+    predicted-ground and GT-ground counts over the points remove_outliers keeps."""
+    pred = np.asarray(pred_labels)
+    sem = np.asarray(sem_label)
+    gt = np.ones(sem.shape)                       # get_GndSeg :95-99
+    gt[np.isin(sem, list(gnd_classes))] = 0
+    gt[np.isin(sem, [0, 1])] = -1
+    keep = (pred >= 0) & (gt >= 0)                # remove_outliers :103-110
+    p, g = 1 - pred[keep], 1 - gt[keep]
+    inter, union = np.logical_and(g, p), np.logical_or(g, p)
+    return np.array([inter.sum(), union.sum(), p.sum(), g.sum()], dtype=np.int64)
+
+
+def masked_mse(pred_gnd, target_gnd, gnd_mask):
+    """evaluate_SemanticKITTI.py:224-226."""
+    mse = (np.square(target_gnd - pred_gnd.T) * gnd_mask).sum()
+    return mse / gnd_mask.sum()

@@ -123,6 +123,28 @@ def main():
         print("array_to_pointcloud2 12-byte rows == compacted obstacle rows:", ok12)
         assert ok12
     gold["pack__points"], gold["pack__labels"], gold["pack__wire16"] = pts, lab, wire16
+    # ---- evaluation reductions (8f row 3): the reference's own get_GndSeg / remove_outliers, lifted out of the
+    # script evaluate_SemanticKITTI.py (module-level argparse / rclpy: not importable) by exec'ing exactly those defs
+    import ast
+    src = open("/root/reference/evaluate_SemanticKITTI.py").read()
+    ns = {"np": np}
+    from numba import jit
+    ns["jit"] = jit
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("get_GndSeg", "remove_outliers"):
+            exec(compile(ast.Module([node], []), "evaluate_SemanticKITTI.py", "exec"), ns)
+    n = 40000
+    sem = rng.choice(np.array([0, 1, 10, 40, 44, 48, 49, 50, 60, 70, 72, 80, 252], dtype=np.uint32), size=n)
+    pred = rng.integers(-1, 2, size=n).astype(np.float64)
+    GndSeg = ns["get_GndSeg"](sem, GndClasses=[40, 44, 48, 49, 60, 72])
+    p2, g2 = ns["remove_outliers"](pred, GndSeg)
+    inter, union = np.logical_and(g2, p2), np.logical_or(g2, p2)
+    ref_counts = np.array([np.sum(inter), np.sum(union), p2.sum(), g2.sum()], dtype=np.int64)
+    ref_metrics = np.array([np.sum(inter) / np.sum(union), np.sum(inter) / p2.sum(), np.sum(inter) / g2.sum()])
+    mine = cpu_ops.ground_counts(pred, sem)
+    print("evaluation counts (I, U, P, G):", ref_counts.tolist(), "oracle equal:", np.array_equal(mine, ref_counts))
+    assert np.array_equal(mine, ref_counts)
+    gold["eval__sem"], gold["eval__pred"], gold["eval__counts"], gold["eval__metrics"] = sem, pred.astype(np.int8), ref_counts, ref_metrics
     if args.write:
         np.savez_compressed(os.path.join(GOLDEN, "cloud_io.npz"), **gold)
         print("wrote tests/golden/cloud_io.npz", sum(v.nbytes for v in gold.values()) // 1024, "KiB raw")

@@ -88,3 +88,31 @@ def test_message_to_labels_chain(cuda):
     assert np.array_equal(got, exp)
     rows = ros_io.pack_segmented(pts[:m].contiguous(), lab[0, :m].contiguous())
     assert rows.cpu().numpy().tobytes() == cpu_ops.pack_segmented(want_cloud, exp).tobytes()
+
+
+def test_eval_metrics(cuda):
+    """evaluation reductions -- integer counts bit-exact against the reference golden and the
+    oracle (1 M points), masked MSE within 1e-12 relative (float64 sums, different association)."""
+    from gndnet_b200 import evaluate
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        sem, pred, want, metrics = z["eval__sem"], z["eval__pred"], z["eval__counts"], z["eval__metrics"]
+    for p in (torch.from_numpy(pred).cuda(), torch.from_numpy(pred.astype(np.float64)).cuda()):
+        got = evaluate.ground_counts(p, torch.from_numpy(sem.view(np.int32)).cuda())
+        assert np.array_equal(got.cpu().numpy(), want)
+    assert np.array_equal(np.array(evaluate.ground_metrics(torch.from_numpy(pred).cuda(), torch.from_numpy(sem.view(np.int32)).cuda())), metrics)
+    rng = np.random.default_rng(9)
+    n = 1_000_003
+    sem2 = rng.choice(np.array([0, 1, 9, 40, 44, 48, 49, 60, 71, 72, 99], dtype=np.uint32), size=n)
+    pred2 = rng.integers(-1, 2, size=n).astype(np.int8)
+    got = evaluate.ground_counts(torch.from_numpy(pred2).cuda(), torch.from_numpy(sem2.view(np.int32)).cuda())
+    assert np.array_equal(got.cpu().numpy(), cpu_ops.ground_counts(pred2, sem2))
+    assert np.array_equal(evaluate.ground_counts(torch.zeros(0, dtype=torch.int8, device="cuda"),
+                                                 torch.zeros(0, dtype=torch.int32, device="cuda")).cpu().numpy(), np.zeros(4, np.int64))
+    # masked MSE on the kitti and (non-square transpose check) a 50 x 40 map
+    for ny, nx in ((100, 100), (40, 50)):
+        pg = rng.standard_normal((ny, nx)).astype(np.float32)
+        tg = rng.standard_normal((nx, ny))
+        mk = (rng.random((nx, ny)) < 0.4).astype(np.float64)
+        want_mse = cpu_ops.masked_mse(pg, tg, mk)
+        got_mse = evaluate.masked_mse(torch.from_numpy(pg).cuda(), torch.from_numpy(tg).cuda(), torch.from_numpy(mk).cuda())
+        assert abs(got_mse - want_mse) <= 1e-12 * abs(want_mse)

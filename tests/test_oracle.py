@@ -82,3 +82,12 @@ def test_pack_segmented_matches_reference_golden():
     with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
         pts, lab, wire = z["pack__points"], z["pack__labels"], z["pack__wire16"]
     assert cpu_ops.pack_segmented(pts, lab).tobytes() == wire.tobytes()
+
+
+def test_eval_counts_match_reference_golden():
+    """get_GndSeg + remove_outliers + the four sums, against the reference functions' output."""
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        sem, pred, want, metrics = z["eval__sem"], z["eval__pred"], z["eval__counts"], z["eval__metrics"]
+    got = cpu_ops.ground_counts(pred.astype(np.float64), sem)
+    assert np.array_equal(got, want)
+    assert np.array_equal(np.array([got[0] / got[1], got[0] / got[2], got[0] / got[3]]), metrics)
