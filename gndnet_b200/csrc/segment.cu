@@ -10,6 +10,7 @@
 // HBM-bound gather: 12-16 B read + 1-8 B written per point, the 40 KB map stays in L1/L2.
 #include "common.cuh"
 #include <limits.h>
+#include <math.h>
 
 namespace gnd {
 
@@ -22,24 +23,25 @@ struct SegArgs {
     const float *elev;
     double *lab64;
     int8_t *lab8;
+    double inv;          // exact reciprocal of voxel_size when it is a power of two, else 0
 };
 
-__device__ __forceinline__ int seg_axis(float v, double lo, double vs, float *shifted) {
+// `inv` != 0: voxel_size is a power of two, so s / vs == s * inv bit for bit and the float64 divide is skipped
+__device__ __forceinline__ int seg_axis(float v, double lo, double vs, double inv, float *shifted) {
     float s = __double2float_rn((double)v - lo);          // :204 (in-place float32 update)
     *shifted = s;
-    double q = floor((double)s / vs);                     // :205-206
+    double q = floor(inv != 0.0 ? (double)s * inv : (double)s / vs);   // :205-206
     if (!(q >= -2147483648.0 && q <= 2147483647.0)) return INT_MIN;   // :207 cvttsd2si semantics
     return (int)q;
 }
 
 __global__ void __launch_bounds__(256) segment_kernel(const SegArgs a) {
-    const int64_t total = (int64_t)a.B * a.N;
     const int F = a.p.num_features;
-    for (int64_t gi = (int64_t)blockIdx.x * 256 + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * 256) {
-        const int b = (int)(gi / a.N);
-        const int64_t i = gi - (int64_t)b * a.N;
+    const int b = blockIdx.y;                              // one grid row per scan: no per-point division
+    const int n = a.counts ? a.counts[b] : (int)a.N;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < a.N; i += (int64_t)gridDim.x * 256) {
+        const int64_t gi = (int64_t)b * a.N + i;
         int label = -1;
-        const int n = a.counts ? a.counts[b] : (int)a.N;
         if (i < n) {
             float *row = a.points + gi * F;
             float x, y, z;
@@ -51,8 +53,8 @@ __global__ void __launch_bounds__(256) segment_kernel(const SegArgs a) {
             }
             if (a.p.apply_z_shift) z = __fadd_rn(z, a.p.z_shift);
             float sx, sy;
-            const int cx = seg_axis(x, a.p.grid_lo[0], a.p.voxel_size, &sx);
-            const int cy = seg_axis(y, a.p.grid_lo[1], a.p.voxel_size, &sy);
+            const int cx = seg_axis(x, a.p.grid_lo[0], a.p.voxel_size, a.inv, &sx);
+            const int cy = seg_axis(y, a.p.grid_lo[1], a.p.voxel_size, a.inv, &sy);
             if (a.p.mutate_points) { row[0] = sx; row[1] = sy; }
             if (0 < cx && cx < a.p.map_nx && 0 < cy && cy < a.p.map_ny) {   // :213
                 const float h = __ldg(a.elev + (int64_t)b * a.p.map_batch_stride + cx * a.p.map_sx + cy * a.p.map_sy);
@@ -117,10 +119,16 @@ int segment_run(const gnd_segment_params *p, float *points, const int32_t *count
     SegArgs a;
     a.p = *p; a.points = points; a.counts = counts; a.B = batch; a.N = n_points;
     a.elev = elevation; a.lab64 = labels_f64; a.lab8 = labels_i8;
-    int64_t total = (int64_t)batch * n_points;
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    segment_kernel<<<blocks, 256, 0, stream>>>(a);
+    {
+        int e = 0;
+        const double m = frexp(p->voxel_size, &e);
+        a.inv = (m == 0.5 && e > -500 && e < 500) ? 1.0 / p->voxel_size : 0.0;
+    }
+    if (batch > 65535) return fail(GND_ERR_UNSUPPORTED, "batch %d > 65535", batch);
+    int gx = (int)((n_points + 255) / 256);
+    const int want = (148 * 16 + batch - 1) / batch;          // ~16 CTAs per SM over the whole grid
+    if (gx > want) gx = want;
+    segment_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
     GND_LAUNCH_CHECK("segment_kernel");
     return GND_OK;
 }

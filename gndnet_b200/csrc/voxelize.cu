@@ -185,19 +185,25 @@ __global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const
             const int i = wbase + VOX_RT_TILE + s * 32 + lane;
             if (i < end) load_xyz(a, a.points + (base + i) * a.F, px[s], py[s], pz[s]);
         }
-        // phase A: in-order ranking inside the warp's 224 points
+        // phase A: in-order ranking inside the warp's 224 points.  The seven match.any are independent of the
+        // counters, so they are issued first (their latency overlaps); only the counter read-modify-write of the
+        // step leaders is serial across steps.
+        unsigned peers[VOX_RT_STEPS];
 #pragma unroll
         for (int s = 0; s < VOX_RT_STEPS; ++s) {
             const unsigned act = __ballot_sync(0xffffffffu, c[s] >= 0);
+            peers[s] = (c[s] >= 0) ? __match_any_sync(act, c[s]) : 0u;
+        }
+#pragma unroll
+        for (int s = 0; s < VOX_RT_STEPS; ++s) {
             r[s] = 0;
             if (c[s] >= 0) {
-                const unsigned peers = __match_any_sync(act, c[s]);
-                const int leader = __ffs(peers) - 1;
+                const int leader = __ffs(peers[s]) - 1;
                 unsigned seen = 0;
                 unsigned char *cnt = reinterpret_cast<unsigned char *>(s_cnt + c[s]) + warp;
-                if (lane == leader) { seen = *cnt; *cnt = (unsigned char)(seen + __popc(peers)); }
-                seen = __shfl_sync(peers, seen, leader);
-                r[s] = (int)seen + __popc(peers & lanemask_lt());
+                if (lane == leader) { seen = *cnt; *cnt = (unsigned char)(seen + __popc(peers[s])); }
+                seen = __shfl_sync(peers[s], seen, leader);
+                r[s] = (int)seen + __popc(peers[s] & lanemask_lt());
             }
             __syncwarp();
         }
