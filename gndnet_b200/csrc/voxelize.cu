@@ -493,7 +493,13 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     // tiled: two CTAs per SM in ONE wave (floor); serial: about two CTAs per SM over the batch
     int64_t k = plan->tiled ? (2 * 148) / batch : (2 * 148 + batch - 1) / batch;
     if (k < 1) k = 1;
-    if (k > VOX_MAX_K) k = VOX_MAX_K;
+    {   // the chunk-histogram table is K x cells: small grids (the 2 500-cell camera grid) afford more, smaller chunks,
+        // so that one dense frame still spreads over every SM
+        int64_t kcap = 655360 / cells;
+        if (kcap < VOX_MAX_K) kcap = VOX_MAX_K;
+        if (kcap > 2 * 148) kcap = 2 * 148;
+        if (k > kcap) k = kcap;
+    }
     if (const char *e = getenv("GNDNET_VOX_K")) { int v = atoi(e); if (v > 0 && v < k) k = v; }
     if (k > kmax) k = kmax;
     if (k < kmin) k = kmin;

@@ -6,7 +6,7 @@ namespace gnd {
 
 constexpr int VOX_SUB = 2048;        // points ranked per sub-tile of a chunk
 constexpr int VOX_MAX_T = 61440;     // chunk size limit: chunk-local counts are uint16
-constexpr int VOX_MAX_K = 64;        // chunks per scan
+constexpr int VOX_MAX_K = 64;        // chunks per scan on big grids (K x cells <= 655 360 lifts it up to 296)
 // tile-parallel ranker: 8 warps x 7 steps x 32 points per tile (per-warp byte counters hold <= 224)
 constexpr int VOX_RT_WARPS = 8;
 constexpr int VOX_RT_STEPS = 7;
