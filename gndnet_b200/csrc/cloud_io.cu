@@ -194,27 +194,51 @@ struct EvalArgs {
     unsigned long long *counts;      // [4]: intersection, union, predicted ground, GT ground
 };
 
+__device__ __forceinline__ void eval_point(const EvalArgs &a, int pred, uint32_t s, unsigned &c_i, unsigned &c_u,
+                                           unsigned &c_p, unsigned &c_g) {
+    bool is_gnd = false;
+    for (int k = 0; k < a.n_classes; ++k) is_gnd |= (s == a.classes[k]);
+    const int gt = (s == 0u || s == 1u) ? -1 : (is_gnd ? 0 : 1);       // the {0,1} assignment comes second (:98-99)
+    if (pred >= 0 && gt >= 0) {
+        const bool pg = pred == 0, gg = gt == 0;
+        c_i += (pg && gg); c_u += (pg || gg); c_p += pg; c_g += gg;
+    }
+}
+
 __global__ void __launch_bounds__(256) eval_counts_kernel(const EvalArgs a) {
     unsigned c_i = 0, c_u = 0, c_p = 0, c_g = 0;
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * 256) {
-        const int pred = a.lab8 ? (int)a.lab8[i] : (int)a.lab64[i];
-        const uint32_t s = __ldg(a.sem + i);
-        bool is_gnd = false;
-        for (int k = 0; k < a.n_classes; ++k) is_gnd |= (s == a.classes[k]);
-        const int gt = (s == 0u || s == 1u) ? -1 : (is_gnd ? 0 : 1);       // the {0,1} assignment comes second (:98-99)
-        if (pred >= 0 && gt >= 0) {
-            const bool pg = pred == 0, gg = gt == 0;
-            c_i += (pg && gg); c_u += (pg || gg); c_p += pg; c_g += gg;
+    const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, nthr = (int64_t)gridDim.x * 256;
+    int64_t done = 0;
+    if (a.lab8 && (((uintptr_t)a.lab8) & 3) == 0 && (((uintptr_t)a.sem) & 15) == 0) {
+        // four points per thread and iteration: one 4-byte label load, one 16-byte class load
+        const int64_t n4 = a.n >> 2;
+        const uint32_t *l4 = reinterpret_cast<const uint32_t *>(a.lab8);
+        const uint4 *s4 = reinterpret_cast<const uint4 *>(a.sem);
+        for (int64_t i = tid; i < n4; i += nthr) {
+            const uint32_t l = __ldg(l4 + i);
+            const uint4 sv = __ldg(s4 + i);
+            eval_point(a, (int)(int8_t)(l & 0xffu), sv.x, c_i, c_u, c_p, c_g);
+            eval_point(a, (int)(int8_t)((l >> 8) & 0xffu), sv.y, c_i, c_u, c_p, c_g);
+            eval_point(a, (int)(int8_t)((l >> 16) & 0xffu), sv.z, c_i, c_u, c_p, c_g);
+            eval_point(a, (int)(int8_t)(l >> 24), sv.w, c_i, c_u, c_p, c_g);
         }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < a.n; i += nthr) {
+        const int pred = a.lab8 ? (int)a.lab8[i] : (int)a.lab64[i];
+        eval_point(a, pred, __ldg(a.sem + i), c_i, c_u, c_p, c_g);
     }
     c_i = __reduce_add_sync(0xffffffffu, c_i); c_u = __reduce_add_sync(0xffffffffu, c_u);
     c_p = __reduce_add_sync(0xffffffffu, c_p); c_g = __reduce_add_sync(0xffffffffu, c_g);
+    // one set of four global atomics per BLOCK: same-address atomics serialise in L2
+    __shared__ unsigned s_c[4];
+    if (threadIdx.x < 4) s_c[threadIdx.x] = 0;
+    __syncthreads();
     if ((threadIdx.x & 31) == 0) {
-        if (c_i) atomicAdd(a.counts + 0, (unsigned long long)c_i);
-        if (c_u) atomicAdd(a.counts + 1, (unsigned long long)c_u);
-        if (c_p) atomicAdd(a.counts + 2, (unsigned long long)c_p);
-        if (c_g) atomicAdd(a.counts + 3, (unsigned long long)c_g);
+        atomicAdd(&s_c[0], c_i); atomicAdd(&s_c[1], c_u); atomicAdd(&s_c[2], c_p); atomicAdd(&s_c[3], c_g);
     }
+    __syncthreads();
+    if (threadIdx.x < 4 && s_c[threadIdx.x]) atomicAdd(a.counts + threadIdx.x, (unsigned long long)s_c[threadIdx.x]);
 }
 
 // one block, fixed reduction tree: the float64 sums are reproducible run to run
