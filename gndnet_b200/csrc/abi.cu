@@ -63,8 +63,10 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
     uint8_t *idx1 = c.take<uint8_t>((size_t)B * H1 * W1 * 128);
     float *regpart = (prec == GND_PREC_FP32) ? nullptr : c.take<float>((size_t)B * H * W * 9);
     int32_t *pfn_ctr = c.take<int32_t>(4);
+    double *bn_partial = cfg.bn_batch_stats ? c.take<double>((size_t)BN_BLOCKS * 256 * 2) : nullptr;
+    float *bn_ab = cfg.bn_batch_stats ? c.take<float>(512) : nullptr;
     if (ws) {
-        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr;
+        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr; ctx->bn_partial = bn_partial; ctx->bn_ab = bn_ab;
         if (names) {
             names->push_back({"idx1", idx1, (size_t)B * H1 * W1 * 128});
             if (regpart) names->push_back({"regpart", regpart, (size_t)B * H * W * 9 * 4});

@@ -10,7 +10,8 @@
 namespace gnd {
 
 constexpr int PFN_OUT = 64;        // cfg.vfe_filters = [64] in every shipped config
-constexpr int PFN_MAX_FEAT = 10;   // F(<=4) + 3 + 2 + with_distance
+constexpr int PFN_MAX_FEAT = 10;
+constexpr int BN_BLOCKS = 592;     // partial-sum blocks of the batch-statistics reduction   // F(<=4) + 3 + 2 + with_distance
 
 // A BEV activation tensor, NHWC ([B][H][W][C]).  fp32 mode: one float plane.  tcgen05 modes: an fp16
 // "hi" plane and (for split-fp16 consumers) an fp16 "lo" plane with value = hi + lo.
@@ -28,7 +29,8 @@ struct ConvLayer {
     float *w32 = nullptr;   // [9][cin][cout] fp32, BatchNorm folded           (fp32 mode)
     __half *whi = nullptr;  // [9][cout][cin] fp16 hi, K-major for UMMA        (tcgen05 modes)
     __half *wlo = nullptr;  // [9][cout][cin] fp16 lo
-    float *bias = nullptr;  // [cout] folded bias
+    float *bias = nullptr;  // [cout] folded bias (raw conv bias in batch-statistics mode)
+    float *gamma = nullptr, *beta = nullptr;   // [cout] BatchNorm2d affine, batch-statistics mode only
     int split = 0;          // tcgen05: 1 = three-product split-fp16, 0 = single fp16 product
 };
 
@@ -66,6 +68,8 @@ struct gnd_ctx {
     gnd::Act canvas, d1a, d1b, p1, d2a, d2b, u2, u2a, u2b, u1, u1a, u1b;
     uint8_t *idx1 = nullptr;   // [B][H1][W1][128] argmax (0..3) of down1's pool
     float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
+    double *bn_partial = nullptr;   // [BN_BLOCKS][256][2] per-block channel sums (batch-statistics mode)
+    float *bn_ab = nullptr;         // [2][256] per-channel scale / shift of the current layer
     int32_t *pfn_ctr = nullptr; // [2] work-queue head + finished-CTA count of pfn_scatter_kernel (self-resetting)
     gnd::TensorMaps *tmaps = nullptr;
     gnd::HaloMaps *hmaps = nullptr;

@@ -351,11 +351,74 @@ static inline int ew_blocks(size_t total) {
     return (int)(b > 148 * 16 ? 148 * 16 : (b < 1 ? 1 : b));
 }
 
+// ---- BatchNorm2d with the statistics of the batch in flight (the module's train-mode arithmetic, segnet.py:35-38
+// left in training mode by predict_ground.py): per-channel mean and biased variance over B*H*W in float64, then
+// y = relu(x * alpha + beta'), alpha = gamma / sqrt(var + eps), beta' = beta - mean * alpha  (eps = 1e-5).
+// Two-stage, fixed-order reduction: reproducible run to run.
+__global__ void __launch_bounds__(256) bn_partial_kernel(const float *__restrict__ x, int64_t npix, int C, double *partial) {
+    __shared__ double s_s[256], s_q[256];
+    const int R = 256 / C;                                   // pixel lanes per channel (C = 64, 128, 256)
+    const int c = threadIdx.x % C, r = threadIdx.x / C;
+    const int64_t per = (npix + gridDim.x - 1) / gridDim.x;
+    const int64_t p0 = (int64_t)blockIdx.x * per, p1 = min(p0 + per, npix);
+    double s = 0.0, q = 0.0;
+    for (int64_t p = p0 + r; p < p1; p += R) {
+        const double v = (double)__ldg(x + p * C + c);
+        s += v; q += v * v;
+    }
+    s_s[threadIdx.x] = s; s_q[threadIdx.x] = q;
+    __syncthreads();
+    if (r == 0) {
+        for (int k = 1; k < R; ++k) { s += s_s[k * C + c]; q += s_q[k * C + c]; }
+        partial[((size_t)blockIdx.x * 256 + c) * 2 + 0] = s;
+        partial[((size_t)blockIdx.x * 256 + c) * 2 + 1] = q;
+    }
+}
+
+__global__ void bn_final_kernel(const double *partial, int nblk, int64_t npix, const float *gamma, const float *beta,
+                                float *ab) {
+    const int c = threadIdx.x;
+    double s = 0.0, q = 0.0;
+    for (int b = 0; b < nblk; ++b) { s += partial[((size_t)b * 256 + c) * 2]; q += partial[((size_t)b * 256 + c) * 2 + 1]; }
+    const double mean = s / (double)npix;
+    double var = q / (double)npix - mean * mean;             // biased variance, as the normalisation uses
+    if (var < 0.0) var = 0.0;
+    const double alpha = (double)gamma[c] / sqrt(var + 1e-5);
+    ab[c] = (float)alpha;
+    ab[256 + c] = (float)((double)beta[c] - mean * alpha);
+}
+
+__global__ void __launch_bounds__(256) bn_apply_relu_kernel(float *x, int64_t n4, int C, const float *__restrict__ ab) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+        const int c = (int)((i * 4) % C);
+        float4 v = reinterpret_cast<float4 *>(x)[i];
+        v.x = fmaxf(fmaf(v.x, ab[c], ab[256 + c]), 0.0f);
+        v.y = fmaxf(fmaf(v.y, ab[c + 1], ab[256 + c + 1]), 0.0f);
+        v.z = fmaxf(fmaf(v.z, ab[c + 2], ab[256 + c + 2]), 0.0f);
+        v.w = fmaxf(fmaf(v.w, ab[c + 3], ab[256 + c + 3]), 0.0f);
+        reinterpret_cast<float4 *>(x)[i] = v;
+    }
+}
+
 static int conv_f32(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int B, cudaStream_t st) {
     const ConvLayer &L = ctx->conv[layer];
+    const bool batch_bn = ctx->cfg.bn_batch_stats != 0;
     dim3 grid(((in.H + 7) / 8) * ((in.W + 7) / 8), L.cout / 64, B);
-    conv3x3_f32_kernel<<<grid, 256, 0, st>>>(in.f32, L.w32, L.bias, out.f32, in.H, in.W, L.cin, L.cout, 1);
+    conv3x3_f32_kernel<<<grid, 256, 0, st>>>(in.f32, L.w32, L.bias, out.f32, in.H, in.W, L.cin, L.cout, batch_bn ? 0 : 1);
     GND_LAUNCH_CHECK("conv3x3_f32_kernel");
+    if (batch_bn) {
+        if (!ctx->bn_partial || !ctx->bn_ab) return fail(GND_ERR_STATE, "workspace has no batch-statistics scratch");
+        const int64_t npix = (int64_t)B * out.H * out.W;
+        int nblk = (int)((npix + 63) / 64);
+        if (nblk > BN_BLOCKS) nblk = BN_BLOCKS;
+        bn_partial_kernel<<<nblk, 256, 0, st>>>(out.f32, npix, L.cout, ctx->bn_partial);
+        GND_LAUNCH_CHECK("bn_partial_kernel");
+        bn_final_kernel<<<1, L.cout, 0, st>>>(ctx->bn_partial, nblk, npix, L.gamma, L.beta, ctx->bn_ab);
+        GND_LAUNCH_CHECK("bn_final_kernel");
+        const int64_t n4 = npix * L.cout / 4;
+        bn_apply_relu_kernel<<<ew_blocks((size_t)n4), 256, 0, st>>>(out.f32, n4, L.cout, ctx->bn_ab);
+        GND_LAUNCH_CHECK("bn_apply_relu_kernel");
+    }
     return GND_OK;
 }
 

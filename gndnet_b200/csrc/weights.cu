@@ -26,6 +26,10 @@ extern "C" int gnd_create(const gnd_config *cfg, int32_t device, gnd_ctx **out) 
         return fail(GND_ERR_UNSUPPORTED, "input_features must be 3 or 4, got %d", cfg->input_features);
     if (cfg->precision < GND_PREC_FP32 || cfg->precision > GND_PREC_SPLIT)
         return fail(GND_ERR_INVALID, "unknown precision %d", cfg->precision);
+    if (cfg->bn_batch_stats && cfg->precision != GND_PREC_FP32)
+        return fail(GND_ERR_UNSUPPORTED, "batch-statistics BatchNorm needs precision fp32 (BatchNorm cannot be folded into the tensor-core weights)");
+    if (cfg->bn_batch_stats && cfg->use_norm)
+        return fail(GND_ERR_UNSUPPORTED, "batch-statistics BatchNorm1d in the pillar encoder (use_norm) is not built");
     int ndev = 0;
     GND_CUDA_CHECK(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(GND_ERR_INVALID, "device %d of %d", device, ndev);
@@ -112,13 +116,16 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
     auto take = [&cur](size_t bytes) { cur = align_up(cur, 256); size_t r = cur; cur += bytes; return r; };
     size_t o_pfn_w = take((size_t)nfeat * PFN_OUT * sizeof(float));
     size_t o_pfn_b = take(PFN_OUT * sizeof(float));
-    size_t o_w[8], o_hi[8], o_lo[8], o_b[8];
+    size_t o_w[8], o_hi[8], o_lo[8], o_b[8], o_g[8], o_be[8];
+    const bool batch_bn = ctx->cfg.bn_batch_stats != 0;
     for (int l = 0; l < 8; ++l) {
         size_t n = (size_t)9 * ctx->conv[l].cin * ctx->conv[l].cout;
         o_w[l] = o_hi[l] = o_lo[l] = 0;
         if (!tc) o_w[l] = take(n * sizeof(float));
         else { o_hi[l] = take(n * sizeof(__half)); o_lo[l] = take(n * sizeof(__half)); }
         o_b[l] = take(ctx->conv[l].cout * sizeof(float));
+        o_g[l] = take(ctx->conv[l].cout * sizeof(float));
+        o_be[l] = take(ctx->conv[l].cout * sizeof(float));
     }
     size_t o_reg_w = take(9 * 64 * sizeof(float));
     size_t o_reg_b = take(sizeof(float));
@@ -162,8 +169,11 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
         const float *var = t.get(p + "1.running_var", cout, &rc);              if (!var) return rc;
         float *db = (float *)(host.data() + o_b[l]);
         for (int co = 0; co < cout; ++co) {
-            const double s = (double)g[co] / sqrt((double)var[co] + 1e-5);
-            db[co] = (float)(((double)b[co] - (double)mu[co]) * s + (double)be[co]);
+            // batch-statistics mode keeps the convolution as it is (weights and bias unscaled) and the affine apart
+            const double s = batch_bn ? 1.0 : (double)g[co] / sqrt((double)var[co] + 1e-5);
+            db[co] = batch_bn ? b[co] : (float)(((double)b[co] - (double)mu[co]) * s + (double)be[co]);
+            ((float *)(host.data() + o_g[l]))[co] = g[co];
+            ((float *)(host.data() + o_be[l]))[co] = be[co];
             for (int ci = 0; ci < cin; ++ci)
                 for (int tap = 0; tap < 9; ++tap) {
                     const float wf = (float)((double)w[((size_t)co * cin + ci) * 9 + tap] * s);
@@ -199,6 +209,8 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
         ctx->conv[l].whi = tc ? (__half *)(d + o_hi[l]) : nullptr;
         ctx->conv[l].wlo = tc ? (__half *)(d + o_lo[l]) : nullptr;
         ctx->conv[l].bias = (float *)(d + o_b[l]);
+        ctx->conv[l].gamma = (float *)(d + o_g[l]);
+        ctx->conv[l].beta = (float *)(d + o_be[l]);
     }
     ctx->reg_w = (float *)(d + o_reg_w);
     ctx->reg_b = (float *)(d + o_reg_b);

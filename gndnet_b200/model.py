@@ -95,12 +95,21 @@ class SegnetGndEst(nn.Module):
 
 
 class GroundEstimatorNet(nn.Module):
-    def __init__(self, cfg, precision=None):
+    def __init__(self, cfg, precision=None, bn_mode="running"):
+        """``bn_mode``: "running" (default) evaluates every BatchNorm2d with its running statistics, i.e. the module
+        after ``.eval()`` as the deployed node runs it (ros_node.py:227); "batch" reproduces the module left in
+        TRAINING mode -- statistics of the batch in flight -- which is what predict_ground.py computes because it
+        never calls ``.eval()``.  "batch" needs ``precision="fp32"``; running buffers are not updated."""
         super().__init__()
         self.cfg = cfg
         self.precision = precision or getattr(cfg, "precision", "mixed")
         if self.precision not in _lib.PRECISIONS:
             raise ValueError("precision must be one of %s" % sorted(_lib.PRECISIONS))
+        if bn_mode not in ("running", "batch"):
+            raise ValueError('bn_mode must be "running" or "batch"')
+        if bn_mode == "batch" and self.precision != "fp32":
+            raise ValueError('bn_mode="batch" needs precision="fp32"')
+        self.bn_mode = bn_mode
         self.voxel_feature_extractor = PillarFeatureNet(
             num_input_features=cfg.input_features, use_norm=cfg.use_norm, num_filters=cfg.vfe_filters,
             with_distance=cfg.with_distance, voxel_size=cfg.voxel_size, pc_range=cfg.pc_range)
@@ -140,6 +149,7 @@ class GroundEstimatorNet(nn.Module):
         c.use_norm = 1 if cfg.use_norm else 0
         c.with_distance = 1 if cfg.with_distance else 0
         c.precision = _lib.PRECISIONS[self.precision]
+        c.bn_batch_stats = 1 if self.bn_mode == "batch" else 0
         return c
 
     def _device(self):
@@ -219,9 +229,10 @@ class GroundEstimatorNet(nn.Module):
             pass
 
     def _check_mode(self):
-        if self.training and not self._warned_train:
+        if self.training and self.bn_mode != "batch" and not self._warned_train:
             warnings.warn("gndnet_b200 evaluates BatchNorm with running statistics (eval mode); the module is in "
-                          "training mode -- call .eval() (predict_ground.py omits it, ros_node.py:227 does not)")
+                          "training mode -- call .eval() (predict_ground.py omits it, ros_node.py:227 does not), or "
+                          'construct with bn_mode="batch", precision="fp32" to reproduce the training-mode arithmetic')
             self._warned_train = True
 
     def buffer(self, name, dtype, shape=None):

@@ -153,6 +153,10 @@ typedef struct gnd_config {
     int32_t use_norm;           /* cfg.use_norm: Linear(no bias)+BatchNorm1d vs Linear(bias)   */
     int32_t with_distance;      /* cfg.with_distance                                          */
     int32_t precision;          /* gnd_precision                                              */
+    int32_t bn_batch_stats;     /* 0: BatchNorm2d with running statistics (eval mode, ros_node.py:227), folded into
+                                   the convolutions.  1: the module's TRAIN-mode arithmetic -- per-channel mean and
+                                   biased variance of the batch being processed -- which is what predict_ground.py
+                                   computes because it never calls .eval() (GND_PREC_FP32 only, use_norm = 0)   */
 } gnd_config;
 
 GND_API int gnd_create(const gnd_config *cfg, int32_t device, gnd_ctx **out);

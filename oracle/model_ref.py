@@ -102,34 +102,40 @@ def pillars_scatter(cfg, voxel_features, coors, batch_size):
     return torch.stack(out, 0).view(batch_size, C, ny, nx)
 
 
-def _cbr(sd, prefix, x):
-    """conv2DBatchNormRelu (segnet.py:11-44): conv3x3 s1 p1 bias -> BN2d(eval) -> ReLU."""
+def _cbr(sd, prefix, x, batch_stats=False):
+    """conv2DBatchNormRelu (segnet.py:11-44): conv3x3 s1 p1 bias -> BN2d -> ReLU.  BN2d in eval mode (running
+    statistics) unless batch_stats: then the module's train-mode arithmetic (per-channel mean / biased variance of
+    this very batch), which is what predict_ground.py runs because it never calls .eval()."""
     x = F.conv2d(x, _t(sd[prefix + ".cbr_unit.0.weight"]), _t(sd[prefix + ".cbr_unit.0.bias"]),
                  stride=1, padding=1)
+    if batch_stats:
+        x = F.batch_norm(x, None, None, _t(sd[prefix + ".cbr_unit.1.weight"]), _t(sd[prefix + ".cbr_unit.1.bias"]),
+                         True, 0.0, BN2D_EPS)
+        return F.relu(x)
     x = F.batch_norm(x, _t(sd[prefix + ".cbr_unit.1.running_mean"]), _t(sd[prefix + ".cbr_unit.1.running_var"]),
                      _t(sd[prefix + ".cbr_unit.1.weight"]), _t(sd[prefix + ".cbr_unit.1.bias"]),
                      False, 0.0, BN2D_EPS)
     return F.relu(x)
 
 
-def segnet(sd, x, return_stages=False):
+def segnet(sd, x, return_stages=False, batch_stats=False):
     """segnetGndEst.forward (segnet.py:133-142).  x [B,64,H,W] -> [B,1,H,W]."""
     e = "encoder_decoder."
     st = {}
-    d1a = _cbr(sd, e + "down1.conv1", x)
-    d1b = _cbr(sd, e + "down1.conv2", d1a)
+    d1a = _cbr(sd, e + "down1.conv1", x, batch_stats)
+    d1b = _cbr(sd, e + "down1.conv2", d1a, batch_stats)
     shape1 = d1b.shape
     p1, i1 = F.max_pool2d(d1b, 2, 2, return_indices=True)          # :54-60
-    d2a = _cbr(sd, e + "down2.conv1", p1)
-    d2b = _cbr(sd, e + "down2.conv2", d2a)
+    d2a = _cbr(sd, e + "down2.conv1", p1, batch_stats)
+    d2b = _cbr(sd, e + "down2.conv2", d2a, batch_stats)
     shape2 = d2b.shape
     p2, i2 = F.max_pool2d(d2b, 2, 2, return_indices=True)
     u2 = F.max_unpool2d(p2, i2, 2, 2, output_size=shape2)          # :84-89
-    u2a = _cbr(sd, e + "up2.conv1", u2)
-    u2b = _cbr(sd, e + "up2.conv2", u2a)
+    u2a = _cbr(sd, e + "up2.conv1", u2, batch_stats)
+    u2b = _cbr(sd, e + "up2.conv2", u2a, batch_stats)
     u1 = F.max_unpool2d(u2b, i1, 2, 2, output_size=shape1)
-    u1a = _cbr(sd, e + "up1.conv1", u1)
-    u1b = _cbr(sd, e + "up1.conv2", u1a)
+    u1a = _cbr(sd, e + "up1.conv1", u1, batch_stats)
+    u1b = _cbr(sd, e + "up1.conv2", u1a, batch_stats)
     out = F.conv2d(u1b, _t(sd[e + "regressor.weight"]), _t(sd[e + "regressor.bias"]), padding=1)   # :131,:140
     if return_stages:
         st.update(d1a=d1a, d1b=d1b, p1=p1, i1=i1, d2a=d2a, d2b=d2b, p2=p2, i2=i2, u2=u2,
@@ -138,14 +144,14 @@ def segnet(sd, x, return_stages=False):
     return out
 
 
-def forward(sd, cfg, voxels, coors, num_points, batch_size=None, return_stages=False):
+def forward(sd, cfg, voxels, coors, num_points, batch_size=None, return_stages=False, bn_batch_stats=False):
     """GroundEstimatorNet.forward (model.py:36-42) in eval mode."""
     B = int(cfg.batch_size if batch_size is None else batch_size)
     with torch.no_grad():
         vf = pillar_feature_net(sd, cfg, voxels, num_points, coors)
         canvas = pillars_scatter(cfg, vf, coors, B)
         if return_stages:
-            out, st = segnet(sd, canvas, True)
+            out, st = segnet(sd, canvas, True, bn_batch_stats)
             st.update(pillar_features=vf, canvas=canvas)
             return torch.squeeze(out), st
-        return torch.squeeze(segnet(sd, canvas))
+        return torch.squeeze(segnet(sd, canvas, False, bn_batch_stats))

@@ -1,0 +1,60 @@
+"""BUILD-CONTAINER ONLY: pins the train-mode-BatchNorm variant of the oracle against the
+unmodified reference model left in training mode -- predict_ground.py's actual behaviour, it never calls .eval() --
+and writes tests/golden/model_heights_train.npz.
+
+    python -m oracle.ref_harness_train [--write]
+"""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--write", action="store_true")
+    args = ap.parse_args()
+    sys.path.insert(0, ROOT)
+    import torch
+    from oracle import cpu_ops, model_ref, synth
+    from oracle.ref_harness import import_reference
+    from tests import cases
+    _, refmodel, _ = import_reference()
+    torch.set_num_threads(8)
+    out = {}
+    for cfgname, names in (("kitti", ["hdl64_s0"]), ("kitti", ["hdl64_s1", "uniform_s0", "real_000000"]),
+                           ("camera", ["small_camera"])):
+        cfg = synth.make_cfg(cfgname, batch_size=len(names))
+        sd = synth.make_state_dict(cfg, 0, synth.load_bn_stats(cfgname))
+        ref = refmodel.GroundEstimatorNet(cfg).cpu()
+        ref.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+        ref.train()                                   # what predict_ground.py leaves the module in
+        vs, cs, ns = [], [], []
+        for b, nm in enumerate(names):
+            raw = cases.load_case(nm)[1]
+            p = raw[:, :cfg.input_features].copy()
+            cpu_ops.shift_cloud(p, cfg.lidar_height)
+            v, c, n = cpu_ops.points_to_voxel(p, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+            vs.append(v); ns.append(n.astype(np.float32))
+            cs.append(np.concatenate([np.full((len(c), 1), b, np.float32), c.astype(np.float32)], 1))
+        v, c, n = np.concatenate(vs), np.concatenate(cs), np.concatenate(ns)
+        with torch.no_grad():
+            r_out = ref(torch.from_numpy(v), torch.from_numpy(c), torch.from_numpy(n))
+        o_out = model_ref.forward(sd, cfg, v, c, n, bn_batch_stats=True)
+        o_eval = model_ref.forward(sd, cfg, v, c, n)
+        d = float((r_out - o_out).abs().max())
+        print("%-8s %-40s |reference(train) - oracle(batch stats)| = %.3g   (train vs eval output differ by %.3g)" %
+              (cfgname, "+".join(names), d, float((o_out - o_eval).abs().max())))
+        assert d <= 1e-5, d
+        out[cfgname + "__" + "_".join(names)] = o_out.numpy().astype(np.float32)
+    if args.write:
+        np.savez_compressed(os.path.join(GOLDEN, "model_heights_train.npz"), **out)
+        print("wrote tests/golden/model_heights_train.npz")
+
+
+if __name__ == "__main__":
+    main()

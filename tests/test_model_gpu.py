@@ -194,3 +194,36 @@ def test_conv_geometries_agree(cfgname, scan, cuda, monkeypatch):
             h, _ = model.infer(pts, threshold=0.08, labels="int8")
             outs[geom] = h.clone()
     assert torch.equal(outs["big"], outs["small"])
+
+
+@pytest.mark.parametrize("cfgname,scans,key", [("kitti", ["hdl64_s0"], "kitti__hdl64_s0"),
+                                               ("kitti", ["hdl64_s1", "uniform_s0", "real_000000"], "kitti__hdl64_s1_uniform_s0_real_000000"),
+                                               ("camera", ["small_camera"], "camera__small_camera")])
+def test_batch_statistics_batchnorm_matches_train_mode_reference(cfgname, scans, key, cuda):
+    """bn_mode="batch" = the reference module left in training mode (predict_ground.py never calls
+    .eval()): per-channel statistics of the batch in flight.  Golden = the unmodified reference in .train() under
+    no_grad (oracle/ref_harness_train.py); the oracle's batch-statistics restatement supplies the stage tensors for
+    the argmax near-tie accounting.  Bar: 1e-3 m (fp32 arithmetic)."""
+    from gndnet_b200.model import GroundEstimatorNet
+    cfg = synth.make_cfg(cfgname, batch_size=len(scans))
+    sd = synth.make_state_dict(cfg, 0, synth.load_bn_stats(cfgname))
+    model = GroundEstimatorNet(cfg, precision="fp32", bn_mode="batch")
+    model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+    model = model.to(cuda)                      # deliberately NOT .eval(): the mode under test
+    raws = [cases.load_case(s)[1] for s in scans]
+    v, c, n, shifted = helpers.oracle_pillars(cfg, raws)
+    ref, st = model_ref.forward(sd, cfg, v, c, n, return_stages=True, bn_batch_stats=True)
+    with torch.no_grad():
+        out = model(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
+    stable_max, frac_masked, overall, flips = helpers.compare_heights(model, out, ref, st)
+    print("%s batch-stat BN: max|dh| unaffected=%.3g overall=%.3g flips=%s masked=%.3f%%" % (key, stable_max, overall, flips, 100 * frac_masked))
+    assert flips[0] <= 1e-4 * st["p1"].numel() + 2 and flips[1] <= 1e-4 * st["p2"].numel() + 2
+    assert stable_max <= 1e-3
+    with np.load(cases.GOLDEN + "/model_heights_train.npz") as z:
+        gold = torch.from_numpy(z[key]).reshape(ref.shape)
+    assert (gold - ref).abs().max().item() <= 2e-5, "oracle (batch statistics) drifted from the reference golden"
+    # and it is a different function from the eval-mode one
+    ref_eval = model_ref.forward(sd, cfg, v, c, n)
+    assert (ref_eval - ref).abs().max().item() > 1e-2
+    with pytest.raises(ValueError):
+        GroundEstimatorNet(cfg, precision="mixed", bn_mode="batch")
