@@ -227,3 +227,26 @@ def test_batch_statistics_batchnorm_matches_train_mode_reference(cfgname, scans,
     assert (ref_eval - ref).abs().max().item() > 1e-2
     with pytest.raises(ValueError):
         GroundEstimatorNet(cfg, precision="mixed", bn_mode="batch")
+
+
+@pytest.mark.parametrize("precision", ["mixed", "fp32"])
+def test_batch_invariance_at_full_size(precision, cuda):
+    """Size-independent property at the bench's own shape: a fused batch of full 120 k-point scans gives, scan by
+    scan, the bytes the same scans give alone (scans never interact: eval-mode BN, per-scan workspaces) -- across the
+    two conv geometries (batch 1 uses the small-batch one) and the batch-dependent chunking of the voxelizer / the
+    work-unit size of the pillar encoder."""
+    cfg = synth.make_cfg("kitti", batch_size=1)
+    model, sd = helpers.load_model(cfg, "kitti", precision, cuda)
+    scans = np.stack([synth.hdl64_scan(500 + s) for s in range(6)] + [synth.uniform_scan(3), synth.uniform_scan(4)])
+    pts = torch.from_numpy(scans).cuda()
+    with torch.no_grad():
+        hb, lb = model.infer(pts, threshold=0.08, labels="int8")
+        hb, lb = hb.clone(), lb.clone()
+        pil_b = {k: v.clone() for k, v in model.pillars(8).items()}
+        for b in range(8):
+            h1, l1 = model.infer(pts[b:b + 1].contiguous(), threshold=0.08, labels="int8")
+            assert torch.equal(h1[0], hb[b]) and torch.equal(l1[0], lb[b]), "scan %d differs inside a batch" % b
+            p1 = model.pillars(1)
+            m = int(p1["voxel_count"][0])
+            assert m == int(pil_b["voxel_count"][b])
+            assert torch.equal(p1["coors"][0, :m], pil_b["coors"][b, :m]) and torch.equal(p1["num_points"][0, :m], pil_b["num_points"][b, :m])

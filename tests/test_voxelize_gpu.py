@@ -110,3 +110,34 @@ def test_nan_points_are_dropped(cuda):
     exp = cpu_ops.points_to_voxel(np.delete(pts, [5, 17], axis=0), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
     for g, e in zip(got, exp):
         assert g.tobytes() == e.tobytes()
+
+
+def test_maximum_sizes(cuda):
+    """The documented envelope: 1.6 M points per scan and 100 000 cells are served bit-exactly (the latter by the
+    one-ranking-warp kernel, grids > 11 264 cells), one more of either is refused loudly -- never a silent fallback."""
+    from gndnet_b200 import _lib
+    from gndnet_b200.point_cloud_ops import points_to_voxel, voxelize_batch
+    rng = np.random.default_rng(77)
+    # 1.6 M points on the kitti grid
+    n = 1_600_000
+    pts = (rng.random((n, 4)) * np.array([110, 110, 9, 1]) - np.array([52, 55, 4.5, 0])).astype(np.float32)
+    got = points_to_voxel(torch.from_numpy(pts).cuda(), [1, 1, 8], [-47, -50, -4, 53, 50, 4], 100, True, 10000)
+    exp = cpu_ops.points_to_voxel(pts, [1, 1, 8], [-47, -50, -4, 53, 50, 4], 100, True, 10000)
+    for g, e in zip(got, exp):
+        assert g.cpu().numpy().tobytes() == e.tobytes()
+    with pytest.raises(_lib.GndError) as ei:
+        voxelize_batch(torch.zeros((1, n + 1, 4), device="cuda"), [1, 1, 8], [-47, -50, -4, 53, 50, 4], 100, 10000)
+    assert ei.value.code == -4
+    # 316 x 316 = 99 856 cells (serial ranking kernel), with max_voxels overflow and max_points truncation
+    n = 300_000
+    pts = (rng.random((n, 3)) * np.array([170, 170, 9]) - np.array([85, 85, 4.5])).astype(np.float32)
+    pts[: n // 4] = pts[n // 4: n // 2] * np.float32(0.05)            # a dense core: cells far beyond max_points
+    vs, cr = [0.5, 0.5, 8], [-79, -79, -4, 79, 79, 4]
+    for mv in (99856, 5000):
+        got = points_to_voxel(pts, vs, cr, 35, True, mv)
+        exp = cpu_ops.points_to_voxel(pts, vs, cr, 35, True, mv)
+        for g, e in zip(got, exp):
+            assert g.shape == e.shape and g.tobytes() == e.tobytes()
+    with pytest.raises(_lib.GndError) as ei:
+        points_to_voxel(pts, [0.5, 0.5, 8], [-79.5, -79, -4, 79, 79, 4], 35, True, 20000)     # 317 x 316 cells
+    assert ei.value.code == -4
