@@ -81,6 +81,9 @@ _SIGS = {
     "gnd_pack_segmented": (ctypes.c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "gnd_eval_ground_counts": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, ctypes.POINTER(ctypes.c_uint32), c_i32, c_vp, c_vp]),
     "gnd_eval_masked_sqerr": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "gnd_raster_workspace_bytes": (ctypes.c_int, [c_i64, ctypes.POINTER(c_d), c_d, c_i32, ctypes.POINTER(c_sz)]),
+    "gnd_lidar_to_img": (ctypes.c_int, [c_vp, c_i64, c_i32, ctypes.POINTER(c_d), c_d, c_d, c_vp, c_vp]),
+    "gnd_lidar_to_heightmap": (ctypes.c_int, [c_vp, c_i64, c_i32, ctypes.POINTER(c_d), c_d, c_i32, c_vp, c_sz, c_vp, c_vp]),
     "gnd_get_buffer": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),
     "gnd_last_launch_count": (ctypes.c_int, [c_vp]),
 }

@@ -54,3 +54,65 @@ def masked_mse(pred_gnd, target_gnd, gnd_mask):
                                            _lib.ptr(sums), _lib.stream_ptr()), "gnd_eval_masked_sqerr")
     s = sums.cpu().numpy()
     return float(s[0] / s[1])
+
+
+# ---------------------------------------------------------------------------------------- ground-truth rasterisation
+def _raster_args(points, grid_size):
+    is_np = isinstance(points, np.ndarray)
+    if is_np:
+        if points.dtype != np.float32 or points.ndim != 2 or points.shape[1] < 3:
+            raise TypeError("points must be float32 [N, >=3]")
+        t = torch.from_numpy(np.ascontiguousarray(points)).cuda()
+    else:
+        if not (points.is_cuda and points.dtype == torch.float32 and points.dim() == 2 and points.shape[1] >= 3):
+            raise TypeError("points must be a float32 [N, >=3] numpy array or CUDA tensor")
+        t = points.contiguous()
+    gs = (ctypes.c_double * 4)(*[float(x) for x in np.asarray(grid_size).reshape(4)])
+    return t, gs, is_np
+
+
+def _map_shape(grid_size, voxel_size):
+    g = np.asarray(grid_size, dtype=np.float64)
+    shp = (g[2:] - g[:2]) / float(voxel_size)
+    return int(shp[0]), int(shp[1])
+
+
+def lidar_to_img(points, grid_size, voxel_size, fill):
+    """utils/utils.py:250-270: [nx, ny] float64 occupancy mask (``fill`` where a point with z + 1.732 < 10 falls).
+    Unlike the numba original it does not overwrite ``points[:, :2]`` (the reference's callers pass a copy)."""
+    t, gs, is_np = _raster_args(points, grid_size)
+    nx, ny = _map_shape(grid_size, voxel_size)
+    with torch.cuda.device(t.device):
+        img = torch.empty((nx, ny), dtype=torch.float64, device=t.device)
+        _lib.check(_lib.lib().gnd_lidar_to_img(_lib.ptr(t), t.shape[0], t.shape[1], gs, float(voxel_size), float(fill),
+                                               _lib.ptr(img), _lib.stream_ptr()), "gnd_lidar_to_img")
+    return img.cpu().numpy() if is_np else img
+
+
+def lidar_to_heightmap(points, grid_size, voxel_size, max_points):
+    """utils/utils.py:273-295: [nx, ny] float64 mean height of the first points of each cell in input order, with the
+    reference's divisor (count + 1) and its one-slot overrun into the next cell reproduced (csrc/raster.cu)."""
+    t, gs, is_np = _raster_args(points, grid_size)
+    nx, ny = _map_shape(grid_size, voxel_size)
+    L = _lib.lib()
+    need = ctypes.c_size_t()
+    with torch.cuda.device(t.device):
+        _lib.check(L.gnd_raster_workspace_bytes(t.shape[0], gs, float(voxel_size), int(max_points), ctypes.byref(need)),
+                   "gnd_raster_workspace_bytes")
+        ws = torch.empty(need.value + 256, dtype=torch.uint8, device=t.device)
+        off = (-ws.data_ptr()) % 256
+        out = torch.empty((nx, ny), dtype=torch.float64, device=t.device)
+        _lib.check(L.gnd_lidar_to_heightmap(_lib.ptr(t), t.shape[0], t.shape[1], gs, float(voxel_size), int(max_points),
+                                            ctypes.c_void_p(ws.data_ptr() + off), need.value, _lib.ptr(out), _lib.stream_ptr()),
+                   "gnd_lidar_to_heightmap")
+    return out.cpu().numpy() if is_np else out
+
+
+def get_target_gnd(cloud, sem_label, grid_range, voxel_size, GndClasses=GND_CLASSES, max_points=100):
+    """evaluate_SemanticKITTI.py:118-127: (gnd_heightmap, gnd_mask) of the points labelled as ground; CUDA tensors."""
+    if cloud.shape[0] != sem_label.shape[0]:
+        raise Exception("Points and label MisMatch")
+    sem = sem_label.to(torch.int64) & 0xFFFFFFFF
+    index = torch.isin(sem, torch.tensor([int(c) for c in GndClasses], device=sem.device))
+    gnd = cloud[index].contiguous()
+    return lidar_to_heightmap(gnd, grid_range, voxel_size, max_points), lidar_to_img(gnd, grid_range, voxel_size, 1)

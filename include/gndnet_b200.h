@@ -252,6 +252,23 @@ GND_API int gnd_eval_ground_counts(const int8_t *labels_i8, const double *labels
 GND_API int gnd_eval_masked_sqerr(const float *pred, const double *target, const double *mask,
                                   int32_t nx, int32_t ny, double *sums2, void *stream);
 
+/*
+ * Ground-truth rasterisation of the evaluation tooling (evaluate_SemanticKITTI.py:118-127).
+ * Maps are [nx][ny] float64 with nx = int((gs[2]-gs[0])/vs), ny = int((gs[3]-gs[1])/vs); h_grid_size4 is a HOST array
+ * (cfg.grid_range as float64).  points [n][num_features] float32 are not modified.
+ * gnd_lidar_to_img        replaces utils/utils.py:250-270 (lidar_to_img).
+ * gnd_lidar_to_heightmap  replaces utils/utils.py:273-295 (lidar_to_heightmap), input-order semantics and the
+ *                         reference's count+1 divisor / one-past-the-end slot write included (see csrc/raster.cu).
+ */
+GND_API int gnd_raster_workspace_bytes(int64_t n_points, const double *h_grid_size4, double voxel_size,
+                                       int32_t max_points, size_t *h_bytes);
+GND_API int gnd_lidar_to_img(const float *points, int64_t n_points, int32_t num_features,
+                             const double *h_grid_size4, double voxel_size, double fill, double *img,
+                             void *stream);
+GND_API int gnd_lidar_to_heightmap(const float *points, int64_t n_points, int32_t num_features,
+                                   const double *h_grid_size4, double voxel_size, int32_t max_points,
+                                   void *workspace, size_t workspace_bytes, double *heightmap, void *stream);
+
 /* Test / profiling hook: device pointer + bytes of a named workspace buffer ("canvas", "coors",
  * "num_points", "voxel_count", "point_offsets", "point_list", "act:<stage>", ...). */
 GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *bytes);

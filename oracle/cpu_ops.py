@@ -181,3 +181,42 @@ def masked_mse(pred_gnd, target_gnd, gnd_mask):
     """evaluate_SemanticKITTI.py:224-226."""
     mse = (np.square(target_gnd - pred_gnd.T) * gnd_mask).sum()
     return mse / gnd_mask.sum()
+
+
+def _map_shape(grid_size, voxel_size):
+    gs = np.asarray(grid_size, dtype=np.float64)
+    shp = (gs[2:] - gs[:2]) / float(voxel_size)           # utils/utils.py:261-262, :284-285 (int() truncation)
+    return int(shp[0]), int(shp[1])
+
+
+def lidar_to_img(points, grid_size, voxel_size, fill):
+    """utils/utils.py:250-270 (does not modify ``points``; the reference is handed a copy)."""
+    L = lib()
+    pts = np.ascontiguousarray(points, dtype=np.float32)
+    nx, ny = _map_shape(grid_size, voxel_size)
+    gs = np.ascontiguousarray(np.asarray(grid_size, dtype=np.float64))
+    img = np.empty((nx, ny), dtype=np.float64)
+    L.gnd_oracle_lidar_to_img.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_int64, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
+                                          ctypes.c_double, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+    L.gnd_oracle_lidar_to_img.restype = None
+    L.gnd_oracle_lidar_to_img(_fp(pts), pts.shape[0], pts.shape[1], gs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                              float(voxel_size), float(fill), nx, ny, img.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+    return img
+
+
+def lidar_to_heightmap(points, grid_size, voxel_size, max_points):
+    """utils/utils.py:273-295, including the one-past-the-end slot write (see gnd_oracle.c)."""
+    L = lib()
+    pts = np.ascontiguousarray(points, dtype=np.float32)
+    nx, ny = _map_shape(grid_size, voxel_size)
+    gs = np.ascontiguousarray(np.asarray(grid_size, dtype=np.float64))
+    slots = np.empty(nx * ny * int(max_points) + 1, dtype=np.float64)
+    num = np.empty(nx * ny, dtype=np.int32)
+    out = np.empty((nx, ny), dtype=np.float64)
+    dp = ctypes.POINTER(ctypes.c_double)
+    L.gnd_oracle_lidar_to_heightmap.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_int64, ctypes.c_int, dp, ctypes.c_double,
+                                                ctypes.c_int, ctypes.c_int, ctypes.c_int, dp, ctypes.POINTER(ctypes.c_int32), dp]
+    L.gnd_oracle_lidar_to_heightmap.restype = ctypes.c_int
+    L.gnd_oracle_lidar_to_heightmap(_fp(pts), pts.shape[0], pts.shape[1], gs.ctypes.data_as(dp), float(voxel_size), int(max_points),
+                                    nx, ny, slots.ctypes.data_as(dp), num.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), out.ctypes.data_as(dp))
+    return out

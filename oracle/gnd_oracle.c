@@ -226,3 +226,65 @@ GND_EXPORT void gnd_oracle_pack_segmented(const float *points, int64_t n, int co
         out[4 * i + 3] = (float)labels[i];
     }
 }
+
+/* ---------------------------------------------------------------------------
+ * SURVEY.md 8(f) row 3, ground-truth rasterisation (evaluate_SemanticKITTI.py:118-127 get_target_gnd):
+ *   utils/utils.py:250-270 lidar_to_img        mask[x, y] = fill for points with float64(z) + 1.732 < 10
+ *   utils/utils.py:273-295 lidar_to_heightmap  mean of the first points of each cell, with the reference's quirks:
+ *     - num_points starts at 1 ("to avoid division by zero") and the divisor is that counter: count + 1;
+ *     - the guard is `k - 1 <= max_points`, so a cell accepts max_points + 1 points and the last one is written to
+ *       heightmap[x, y, max_points] -- one past the cell's slots.  numba does not bounds-check: in C order that is
+ *       slot 0 of the NEXT cell (x, y + 1) (or (x + 1, 0)), which keeps whichever write came last in input order.
+ *       For the very last cell the write leaves the array (real undefined behaviour): dropped here.
+ * Cell arithmetic as in segment_cloud (:204-207): float32(p - lo), float64 divide by the Python scalar, floor, and the
+ * exclusive test 0 < x < nx, 0 < y < ny.  points [n][cols] float32 (not modified); out maps [nx][ny] float64.
+ * ------------------------------------------------------------------------- */
+static int gnd_oracle_cell(float v, double lo, double vs, int n_axis)
+{
+    volatile float s = (float)((double)v - lo);
+    double q = floor((double)s / vs);
+    if (!(q > 0.0 && q < (double)n_axis)) return -1;
+    return (int)q;
+}
+
+GND_EXPORT void gnd_oracle_lidar_to_img(const float *points, int64_t n, int cols, const double *grid_size4,
+                                        double voxel_size, double fill, int nx, int ny, double *img)
+{
+    for (int64_t c = 0; c < (int64_t)nx * ny; ++c) img[c] = 0.0;
+    for (int64_t i = 0; i < n; ++i) {
+        const float *p = points + i * cols;
+        if (!((double)p[2] + 1.732 < 10.0)) continue;
+        int x = gnd_oracle_cell(p[0], grid_size4[0], voxel_size, nx);
+        int y = gnd_oracle_cell(p[1], grid_size4[1], voxel_size, ny);
+        if (x < 0 || y < 0) continue;
+        img[(int64_t)x * ny + y] = fill;
+    }
+}
+
+GND_EXPORT int gnd_oracle_lidar_to_heightmap(const float *points, int64_t n, int cols, const double *grid_size4,
+                                             double voxel_size, int max_points, int nx, int ny, double *slots /* scratch
+                                             [nx*ny*max_points + 1] */, int32_t *num /* scratch [nx*ny] */, double *out)
+{
+    const int64_t cells = (int64_t)nx * ny;
+    for (int64_t k = 0; k < cells * max_points + 1; ++k) slots[k] = 0.0;
+    for (int64_t c = 0; c < cells; ++c) num[c] = 1;
+    for (int64_t i = 0; i < n; ++i) {
+        const float *p = points + i * cols;
+        if (!(p[2] < 10.0f)) continue;
+        int x = gnd_oracle_cell(p[0], grid_size4[0], voxel_size, nx);
+        int y = gnd_oracle_cell(p[1], grid_size4[1], voxel_size, ny);
+        if (x < 0 || y < 0) continue;
+        const int64_t c = (int64_t)x * ny + y;
+        const int k = num[c];
+        if (k - 1 <= max_points) {
+            slots[c * max_points + (k - 1)] = (double)p[2];      /* k - 1 == max_points lands in the next cell's slot 0 */
+            num[c] += 1;
+        }
+    }
+    for (int64_t c = 0; c < cells; ++c) {
+        double s = 0.0;
+        for (int k = 0; k < max_points; ++k) s += slots[c * max_points + k];
+        out[c] = s / (double)num[c];
+    }
+    return 0;
+}

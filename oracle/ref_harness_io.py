@@ -145,6 +145,23 @@ def main():
     print("evaluation counts (I, U, P, G):", ref_counts.tolist(), "oracle equal:", np.array_equal(mine, ref_counts))
     assert np.array_equal(mine, ref_counts)
     gold["eval__sem"], gold["eval__pred"], gold["eval__counts"], gold["eval__metrics"] = sem, pred.astype(np.int8), ref_counts, ref_metrics
+    # ---- ground-truth rasterisation (8f row 3): the reference's numba lidar_to_img / lidar_to_heightmap as they are
+    from oracle import synth
+    cfgk = synth.make_cfg("kitti")
+    gr = np.asarray(cfgk.grid_range)
+    with np.load(os.path.join(GOLDEN, "real_000000.npz")) as z:
+        real = z["points"].astype(np.float32)[:, :3].copy()       # cells with up to ~1000 points: the overrun is exercised
+    hd = synth.hdl64_scan(3)[:, :3].copy()
+    hd[:, 2] += np.float32(1.733)
+    for name, pts, mp in (("real", real, 100), ("hdl64", hd, 100), ("hdl64_mp5", hd, 5)):
+        r_img = utils.lidar_to_img(np.copy(pts), gr, cfgk.voxel_size[0], fill=1)
+        r_h = utils.lidar_to_heightmap(np.copy(pts), gr, cfgk.voxel_size[0], max_points=mp)
+        o_img = cpu_ops.lidar_to_img(pts, gr, cfgk.voxel_size[0], 1)
+        o_h = cpu_ops.lidar_to_heightmap(pts, gr, cfgk.voxel_size[0], mp)
+        d = float(np.abs(r_h - o_h).max())
+        print("rasterisation %-10s img equal %s, heightmap max|d| %.3g" % (name, np.array_equal(r_img, o_img), d))
+        assert np.array_equal(r_img, o_img) and d <= 1e-12
+        gold["raster__%s__img" % name], gold["raster__%s__height" % name] = r_img.astype(np.uint8), r_h
     if args.write:
         np.savez_compressed(os.path.join(GOLDEN, "cloud_io.npz"), **gold)
         print("wrote tests/golden/cloud_io.npz", sum(v.nbytes for v in gold.values()) // 1024, "KiB raw")

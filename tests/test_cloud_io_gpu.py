@@ -116,3 +116,40 @@ def test_eval_metrics(cuda):
         want_mse = cpu_ops.masked_mse(pg, tg, mk)
         got_mse = evaluate.masked_mse(torch.from_numpy(pg).cuda(), torch.from_numpy(tg).cuda(), torch.from_numpy(mk).cuda())
         assert abs(got_mse - want_mse) <= 1e-12 * abs(want_mse)
+
+
+@pytest.mark.parametrize("name,mp", [("real", 100), ("hdl64", 100), ("hdl64_mp5", 5)])
+def test_rasterisation(name, mp, cuda):
+    """GT rasterisation on the device against the reference goldens and the oracle; numpy in ->
+    numpy out and CUDA in -> CUDA out; inputs untouched."""
+    from gndnet_b200 import evaluate
+    from tests.test_oracle import _raster_points
+    cfg = synth.make_cfg("kitti")
+    gr = np.asarray(cfg.grid_range)
+    pts = _raster_points(name)
+    keep = pts.copy()
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        img, hm = z["raster__%s__img" % name].astype(np.float64), z["raster__%s__height" % name]
+    assert np.array_equal(evaluate.lidar_to_img(pts, gr, cfg.voxel_size[0], 1), img)
+    got = evaluate.lidar_to_heightmap(pts, gr, cfg.voxel_size[0], mp)
+    assert got.shape == hm.shape and np.abs(got - hm).max() <= 1e-12
+    assert np.array_equal(pts, keep)
+    g2 = evaluate.lidar_to_heightmap(torch.from_numpy(pts).cuda(), gr, cfg.voxel_size[0], mp)
+    assert g2.is_cuda and np.array_equal(g2.cpu().numpy(), got)
+
+
+def test_rasterisation_random_and_edges(cuda):
+    from gndnet_b200 import evaluate
+    rng = np.random.default_rng(12)
+    for gr, vs, mp, n in (([0, -5, 10, 5], 0.2, 100, 300000), ([-50, -50, 50, 50], 1, 3, 50000), ([-10, -20, 30, 20], 0.5, 1, 1),
+                          ([-50, -50, 50, 50], 1, 100, 0)):
+        gr = np.asarray(gr)
+        pts = (rng.random((n, 4)) * np.array([gr[2] - gr[0] + 4, gr[3] - gr[1] + 4, 16, 1]) + np.array([gr[0] - 2, gr[1] - 2, -4, 0])).astype(np.float32)
+        if n > 1000:      # keep the very last cell below max_points + 1 points (undefined in the reference beyond that)
+            nx, ny = int((gr[2] - gr[0]) / vs), int((gr[3] - gr[1]) / vs)
+            last = (np.floor((pts[:, 0] - np.float32(gr[0])).astype(np.float64) / vs) == nx - 1) & \
+                   (np.floor((pts[:, 1] - np.float32(gr[1])).astype(np.float64) / vs) == ny - 1)
+            pts = pts[~last]
+        assert np.array_equal(evaluate.lidar_to_img(pts, gr, vs, 1), cpu_ops.lidar_to_img(pts, gr, vs, 1))
+        a, b = evaluate.lidar_to_heightmap(pts, gr, vs, mp), cpu_ops.lidar_to_heightmap(pts, gr, vs, mp)
+        assert a.shape == b.shape and np.abs(a - b).max() <= 1e-12

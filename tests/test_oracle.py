@@ -91,3 +91,25 @@ def test_eval_counts_match_reference_golden():
     got = cpu_ops.ground_counts(pred.astype(np.float64), sem)
     assert np.array_equal(got, want)
     assert np.array_equal(np.array([got[0] / got[1], got[0] / got[2], got[0] / got[3]]), metrics)
+
+
+@pytest.mark.parametrize("name,mp", [("real", 100), ("hdl64", 100), ("hdl64_mp5", 5)])
+def test_rasterisation_matches_reference_golden(name, mp):
+    """lidar_to_img / lidar_to_heightmap (one-slot overrun into the next cell included) against the
+    maps the reference's numba functions produced."""
+    cfg = synth.make_cfg("kitti")
+    pts = _raster_points(name)
+    with np.load(cases.GOLDEN + "/cloud_io.npz") as z:
+        img, hm = z["raster__%s__img" % name], z["raster__%s__height" % name]
+    gr = np.asarray(cfg.grid_range)
+    assert np.array_equal(cpu_ops.lidar_to_img(pts, gr, cfg.voxel_size[0], 1), img.astype(np.float64))
+    assert np.abs(cpu_ops.lidar_to_heightmap(pts, gr, cfg.voxel_size[0], mp) - hm).max() <= 1e-12
+
+
+def _raster_points(name):
+    if name == "real":
+        with np.load(cases.GOLDEN + "/real_000000.npz") as z:
+            return z["points"].astype(np.float32)[:, :3].copy()
+    pts = synth.hdl64_scan(3)[:, :3].copy()
+    pts[:, 2] += np.float32(1.733)
+    return pts
