@@ -30,7 +30,17 @@ constexpr int H2_THREADS = 256;
 constexpr int H2_SA = 2;
 constexpr int H2_MAX_SB = 8;
 constexpr int H2_NBARS = 2 * H2_SA + 2 * H2_MAX_SB + 4;
-constexpr int H2_RING_BUDGET = 222 * 1024;
+#ifndef H2_RING_KB
+#define H2_RING_KB 222
+#endif
+#ifndef H2_MINBLOCKS
+#define H2_MINBLOCKS 1          // keep 1: at 255 registers x 256 threads a CTA owns its SM, so two pair kernels from
+                                // different streams can never be co-resident.  With 2 (128 registers) they can, and then
+                                // deadlock: each holds the 512 TMEM columns of one SM of the other's CTA pair while
+                                // blocking in tcgen05.alloc for its own (measured: a two-context run hung; the convs
+                                // were also 12 % slower with the 120 KB ring that co-residency would need)
+#endif
+constexpr int H2_RING_BUDGET = H2_RING_KB * 1024;
 
 struct Halo2Params {
     int H, W, Cout, B;
@@ -161,7 +171,7 @@ __device__ __forceinline__ void h2_issue_tap(uint32_t d0, int tiles, uint32_t NT
     }
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(H2_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(H2_THREADS, H2_MINBLOCKS)
 conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
                      const __grid_constant__ CUtensorMap tm_b_hi, const __grid_constant__ CUtensorMap tm_b_lo,
                      const Halo2Params p) {
