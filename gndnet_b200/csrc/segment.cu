@@ -24,6 +24,7 @@ struct SegArgs {
     double *lab64;
     int8_t *lab8;
     double inv;          // exact reciprocal of voxel_size when it is a power of two, else 0
+    int32_t quad;        // 16-byte rows, N % 4 == 0 and aligned outputs: four points per thread
 };
 
 // `inv` != 0: voxel_size is a power of two, so s / vs == s * inv bit for bit and the float64 divide is skipped
@@ -35,31 +36,53 @@ __device__ __forceinline__ int seg_axis(float v, double lo, double vs, double in
     return (int)q;
 }
 
+// label of one point whose row has been loaded (x, y, z): writes the shifted x, y back when asked (:204)
+__device__ __forceinline__ int seg_label(const SegArgs &a, int b, float *row, float x, float y, float z) {
+    if (a.p.apply_z_shift) z = __fadd_rn(z, a.p.z_shift);
+    float sx, sy;
+    const int cx = seg_axis(x, a.p.grid_lo[0], a.p.voxel_size, a.inv, &sx);
+    const int cy = seg_axis(y, a.p.grid_lo[1], a.p.voxel_size, a.inv, &sy);
+    if (a.p.mutate_points) { row[0] = sx; row[1] = sy; }
+    if (0 < cx && cx < a.p.map_nx && 0 < cy && cy < a.p.map_ny) {   // :213
+        const float h = __ldg(a.elev + (int64_t)b * a.p.map_batch_stride + cx * a.p.map_sx + cy * a.p.map_sy);
+        return ((double)z > (double)h + a.p.threshold) ? 1 : 0;     // :214-217
+    }
+    return -1;
+}
+
 __global__ void __launch_bounds__(256) segment_kernel(const SegArgs a) {
     const int F = a.p.num_features;
     const int b = blockIdx.y;                              // one grid row per scan: no per-point division
     const int n = a.counts ? a.counts[b] : (int)a.N;
+    if (a.quad) {
+        // four consecutive points per thread: the four 16-byte row loads are in flight together, the four int8
+        // labels leave as one 4-byte store
+        for (int64_t i = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4; i < a.N; i += (int64_t)gridDim.x * 1024) {
+            const int64_t gi = (int64_t)b * a.N + i;
+            float4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                v[k] = (i + k < n) ? *reinterpret_cast<const float4 *>(a.points + (gi + k) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            int lab[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                lab[k] = (i + k < n) ? seg_label(a, b, a.points + (gi + k) * 4, v[k].x, v[k].y, v[k].z) : -1;
+            if (a.lab8)
+                *reinterpret_cast<uint32_t *>(a.lab8 + gi) = (uint32_t)(uint8_t)lab[0] | ((uint32_t)(uint8_t)lab[1] << 8) |
+                                                             ((uint32_t)(uint8_t)lab[2] << 16) | ((uint32_t)(uint8_t)lab[3] << 24);
+            if (a.lab64) {
+                *reinterpret_cast<double2 *>(a.lab64 + gi) = make_double2((double)lab[0], (double)lab[1]);
+                *reinterpret_cast<double2 *>(a.lab64 + gi + 2) = make_double2((double)lab[2], (double)lab[3]);
+            }
+        }
+        return;
+    }
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < a.N; i += (int64_t)gridDim.x * 256) {
         const int64_t gi = (int64_t)b * a.N + i;
         int label = -1;
         if (i < n) {
             float *row = a.points + gi * F;
-            float x, y, z;
-            if (F == 4 && (((uintptr_t)a.points) & 15) == 0) {
-                float4 v = *reinterpret_cast<const float4 *>(row);
-                x = v.x; y = v.y; z = v.z;
-            } else {
-                x = row[0]; y = row[1]; z = row[2];
-            }
-            if (a.p.apply_z_shift) z = __fadd_rn(z, a.p.z_shift);
-            float sx, sy;
-            const int cx = seg_axis(x, a.p.grid_lo[0], a.p.voxel_size, a.inv, &sx);
-            const int cy = seg_axis(y, a.p.grid_lo[1], a.p.voxel_size, a.inv, &sy);
-            if (a.p.mutate_points) { row[0] = sx; row[1] = sy; }
-            if (0 < cx && cx < a.p.map_nx && 0 < cy && cy < a.p.map_ny) {   // :213
-                const float h = __ldg(a.elev + (int64_t)b * a.p.map_batch_stride + cx * a.p.map_sx + cy * a.p.map_sy);
-                label = ((double)z > (double)h + a.p.threshold) ? 1 : 0;     // :214-217
-            }
+            label = seg_label(a, b, row, row[0], row[1], row[2]);
         }
         if (a.lab8) a.lab8[gi] = (int8_t)label;
         if (a.lab64) a.lab64[gi] = (double)label;
@@ -125,7 +148,9 @@ int segment_run(const gnd_segment_params *p, float *points, const int32_t *count
         a.inv = (m == 0.5 && e > -500 && e < 500) ? 1.0 / p->voxel_size : 0.0;
     }
     if (batch > 65535) return fail(GND_ERR_UNSUPPORTED, "batch %d > 65535", batch);
-    int gx = (int)((n_points + 255) / 256);
+    a.quad = (p->num_features == 4 && (n_points & 3) == 0 && (((uintptr_t)points) & 15) == 0 &&
+              (!labels_i8 || (((uintptr_t)labels_i8) & 3) == 0) && (!labels_f64 || (((uintptr_t)labels_f64) & 15) == 0)) ? 1 : 0;
+    int gx = (int)((n_points + (a.quad ? 1023 : 255)) / (a.quad ? 1024 : 256));
     const int want = (148 * 16 + batch - 1) / batch;          // ~16 CTAs per SM over the whole grid
     if (gx > want) gx = want;
     segment_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
