@@ -131,11 +131,12 @@ __device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s
 // host so that max_points * half a voxel fits 31 bits): one integer warp reduction (redux.sync) per axis
 // instead of a 5-level float shuffle tree, and an error (<= 2^-25 of a voxel per point) far below the float32
 // summation error of the reference's own mean.
+template <bool DIST, bool HAS_R>
 __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const PfnArgs a) {
     __shared__ float4 s_pt[PFN_WARPS][32];
     __shared__ float s_dist[PFN_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int kf = a.F > 3 ? 4 : 3;
+    constexpr int kf = HAS_R ? 4 : 3;
     auto W = [&](int k, int ch) { return __ldg(a.w + k * PFN_OUT + ch); };
     const int ch0 = 2 * lane, ch1 = 2 * lane + 1;
     const float wx0 = W(0, ch0), wx1 = W(0, ch1), wy0 = W(1, ch0), wy1 = W(1, ch1);
@@ -144,8 +145,8 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
     const float A0 = wx0 + wmx0 + W(kf + 3, ch0), A1 = wx1 + wmx1 + W(kf + 3, ch1);
     const float B0 = wy0 + wmy0 + W(kf + 4, ch0), B1 = wy1 + wmy1 + W(kf + 4, ch1);
     const float C0 = W(2, ch0) + wmz0, C1 = W(2, ch1) + wmz1;
-    const float D0 = kf == 4 ? W(3, ch0) : 0.0f, D1 = kf == 4 ? W(3, ch1) : 0.0f;
-    const float G0 = a.with_distance ? W(kf + 5, ch0) : 0.0f, G1 = a.with_distance ? W(kf + 5, ch1) : 0.0f;
+    const float D0 = HAS_R ? W(3, ch0) : 0.0f, D1 = HAS_R ? W(3, ch1) : 0.0f;
+    const float G0 = DIST ? W(kf + 5, ch0) : 0.0f, G1 = DIST ? W(kf + 5, ch1) : 0.0f;
     const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
     const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
     const int cells = a.nx * a.ny;
@@ -201,11 +202,11 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
                         float4 p = p0;
                         if (q0 != 0) { p = __ldg(pts + o + q0 + lane); f = make_float4(p.x - pcx, p.y - pcy, p.z, p.w); }
                         s_pt[warp][lane] = f;
-                        if (a.with_distance) s_dist[warp][lane] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p.x, p.x), __fmul_rn(p.y, p.y)), __fmul_rn(p.z, p.z)));
+                        if (DIST) s_dist[warp][lane] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p.x, p.x), __fmul_rn(p.y, p.y)), __fmul_rn(p.z, p.z)));
                     }
                     __syncwarp();
                     const int cnt = min(32, n - q0);
-                    if (a.with_distance) {
+                    if (DIST) {
                         for (int q = 0; q < cnt; ++q) {
                             const float4 f = s_pt[warp][q];
                             const float dq = s_dist[warp][q];
@@ -216,8 +217,13 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
 #pragma unroll 4
                         for (int q = 0; q < cnt; ++q) {
                             const float4 f = s_pt[warp][q];
-                            t0 = fmaxf(t0, fmaf(D0, f.w, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x))));
-                            t1 = fmaxf(t1, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x))));
+                            if (HAS_R) {
+                                t0 = fmaxf(t0, fmaf(D0, f.w, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x))));
+                                t1 = fmaxf(t1, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x))));
+                            } else {
+                                t0 = fmaxf(t0, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x)));
+                                t1 = fmaxf(t1, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x)));
+                            }
                         }
                     }
                     __syncwarp();
@@ -332,7 +338,14 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     int64_t warps = (cells_all + (1 << a.gshift) - 1) >> a.gshift;
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically
-    pfn_scatter_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+    const bool has_r = ctx->cfg.input_features > 3;
+    if (ctx->cfg.with_distance) {
+        if (has_r) pfn_scatter_kernel<true, true><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+        else pfn_scatter_kernel<true, false><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+    } else {
+        if (has_r) pfn_scatter_kernel<false, true><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+        else pfn_scatter_kernel<false, false><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+    }
     GND_LAUNCH_CHECK("pfn_scatter_kernel");
     return GND_OK;
 }
