@@ -175,6 +175,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(H2_THREADS, H2_MINBL
 conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
                      const __grid_constant__ CUtensorMap tm_b_hi, const __grid_constant__ CUtensorMap tm_b_lo,
                      const Halo2Params p) {
+#ifdef HALO_STATS
+    const long long t_entry = clock64();
+#endif
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t *ring_a = smem;
@@ -268,6 +271,7 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
             uint32_t pha = 0, phb = 0, phacc = 0;
 #ifdef HALO_STATS
             long long st[4] = {0, 0, 0, 0}; const long long tstart = clock64();
+            atomicAdd(&g_h2_stats[4], (unsigned long long)(tstart - t_entry));      // prologue: entry -> issuer ready
 #endif
             for (int item = pair; item < p.pair_items; item += n_pairs) {
                 const int j = item / p.n_ntiles;
@@ -387,6 +391,9 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();          // the peer's shared memory and barriers stay alive until the leader's last MMA / commit
+#ifdef HALO_STATS
+    if (leader && threadIdx.x == 0) atomicAdd(&g_h2_stats[5], (unsigned long long)(clock64() - t_entry));   // whole CTA lifetime
+#endif
     if (warp == 2) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
@@ -554,8 +561,8 @@ int halo2_conv_run(gnd_ctx *ctx, int l, const Act &out, int B, bool fuse_regress
         cudaStreamSynchronize(st);
         cudaMemcpyFromSymbol(h, g_h2_stats, sizeof(h));
         const double g = (double)pairs;
-        fprintf(stderr, "halo2 layer %d: per-pair clks: issuer total %.0f wait_tempty %.0f wait_afull %.0f wait_bfull %.0f | items/pair %.1f\n",
-                l, h[3] / g, h[0] / g, h[1] / g, h[2] / g, p.pair_items / g);
+        fprintf(stderr, "halo2 layer %d: per-pair clks: issuer total %.0f wait_tempty %.0f wait_afull %.0f wait_bfull %.0f | items/pair %.1f | prologue %.0f cta lifetime %.0f\n",
+                l, h[3] / g, h[0] / g, h[1] / g, h[2] / g, p.pair_items / g, h[4] / g, h[5] / g);
         unsigned long long z[8] = {0};
         cudaMemcpyToSymbol(g_h2_stats, z, sizeof(z));
     }
