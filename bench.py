@@ -139,7 +139,7 @@ def cpu_baseline(seconds, warm=2, pool=16):
     """The CPU path on a bounded sample: distinct synthetic scans (a pool of `pool`, cycled) until `seconds`
     of CPU work have been timed."""
     import torch
-    from oracle import synth
+    from gndnet_b200 import synth
     use_all_host_threads()
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
@@ -164,7 +164,8 @@ def torch_cuda_baseline(seconds=3.0):
     pageable H2D of the dense [M,100,4] voxels -> eager PyTorch CUDA forward (cuDNN, torch's default TF32 policy)
     -> D2H of the map -> CPU segment_cloud, one scan at a time; plus the forward alone on resident tensors."""
     import torch
-    from oracle import cpu_ops, model_ref, synth
+    from oracle import cpu_ops, model_ref
+    from gndnet_b200 import synth
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -216,7 +217,7 @@ def run_reference(args, rank):
     cfgd = {"workload": "GndNet kittiSem inference, synthetic 120k-point HDL-64 scans, streaming batch %d per GPU" % args.batch,
             "points_per_scan": N_POINTS, "batch_per_gpu": args.batch,
             "sample_per_step": "%d scans of the batch (bounded sample), one at a time like predict_ground.py" % args.ref_scans_per_step}
-    from oracle import synth
+    from gndnet_b200 import synth
     use_all_host_threads()
     cfg = synth.make_cfg("kitti")
     sd, ck = synth.checkpoint("kitti")

@@ -64,11 +64,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--write", action="store_true")
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--verify", action="store_true",
+                    help="regenerate every fixture in memory and require equality with the committed tests/golden/ files")
     args = ap.parse_args()
 
     import torch
     sys.path.insert(0, ROOT)
-    from oracle import cpu_ops, model_ref, synth
+    from oracle import cpu_ops, model_ref
+    from gndnet_b200 import synth
 
     ops, refmodel, refutils = import_reference()
     torch.set_num_threads(8)
@@ -197,7 +200,8 @@ def main():
             with torch.no_grad():
                 vf = model_ref.pillar_feature_net(sd0, cfg, v, n, c)
                 canvas = model_ref.pillars_scatter(cfg, vf, c, cfg.batch_size)
-            stats = synth.calibrate(cfg, canvas.numpy(), 0)
+            from oracle.calibrate import calibrate
+            stats = calibrate(cfg, canvas.numpy(), 0)
             if args.write:
                 np.savez(path, **stats)
                 print("[wrote]", path)
@@ -206,7 +210,11 @@ def main():
     model_golden = {}
     model_arrays = {}
     model_cases = [("kitti", ["hdl64_s0"], {}), ("kitti", ["hdl64_s1", "uniform_s0", "real_000000"], {}),
-                   ("camera", ["small_camera"], {}), ("kitti", ["small_kitti"], dict(use_norm=True))]
+                   ("camera", ["small_camera"], {}), ("kitti", ["small_kitti"], dict(use_norm=True)),
+                   # BASELINE configs[4]: max_voxels overflow (the loop's break, point_cloud_ops.py:44-45) through the model
+                   ("kitti", ["overflow_1000"], dict(max_voxels=1000))]
+    if not args.quick:   # BASELINE configs[3]: the dense 1 M-point camera frame, 50 -> 25 -> 12 pooling
+        model_cases.append(("camera", ["camera_1m"], {}))
     raw_by_name = {n: r for n, _, r, _ in cases}
     for cfgname, names, ov in model_cases:
         cfg = synth.make_cfg(cfgname, batch_size=len(names), **ov)
@@ -225,8 +233,8 @@ def main():
         d_cv = float((r_canvas - st["canvas"]).abs().max())
         d_out = float((r_out - o_out).abs().max())
         assert d_vf == 0.0 and d_cv == 0.0 and d_out <= 1e-6, (names, d_vf, d_cv, d_out)
-        key = cfgname + ":" + "+".join(names) + ("+norm" if ov else "")
-        o = o_out.numpy()
+        key = cfgname + ":" + "+".join(names) + ("+norm" if "use_norm" in ov else "")
+        o = r_out.numpy().reshape(o_out.shape)          # the REFERENCE's heights are the golden (oracle == them to 1e-6)
         model_golden[key] = dict(cfg=cfgname, scans=names, overrides=ov, M=int(len(n)),
                                  height_mean=float(o.mean()), height_std=float(o.std()),
                                  height_min=float(o.min()), height_max=float(o.max()),
@@ -234,12 +242,46 @@ def main():
                                                  absmax=float(t.float().abs().max()))
                                          for k, t in st.items() if k not in ("i1", "i2")})
         model_arrays[key.replace(":", "__").replace("+", "_")] = o.astype(np.float32)
+        # per-point labels of the whole reference call sequence (predict_ground.py:110-121, :165-168) on these scans
+        lab_digest = []
+        for b, x in enumerate(names):
+            p_ = raw_by_name[x][:, :cfg.input_features].copy()
+            ref_shift(p_, np.float32(cfg.lidar_height))
+            hb = o.reshape(len(names), *o.shape[-2:])[b]
+            lr = refutils.segment_cloud(p_.copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0], elevation_map=hb.T, threshold=0.08)
+            lab_digest.append(dict(digest=synth.digest(lr.astype(np.int8)), counts=[int((lr == q).sum()) for q in (-1, 0, 1)]))
+        model_golden[key]["labels_thr0.08"] = lab_digest
         print("[model ok] %-40s M=%6d |d_pfn|=%g |d_canvas|=%g |d_out|=%g  height std=%.3f range=[%.3f,%.3f]" %
               (key, len(n), d_vf, d_cv, d_out, o.std(), o.min(), o.max()))
         for k, t in st.items():
             if k not in ("i1", "i2"):
                 print("      %-16s absmax=%9.3f std=%8.3f" % (k, float(t.float().abs().max()), float(t.float().std())))
 
+    if args.verify:
+        with open(os.path.join(GOLDEN, "voxel_cases.json")) as f:
+            assert json.load(f) == json.loads(json.dumps(vox_golden)), "voxel_cases.json is stale"
+        with open(os.path.join(GOLDEN, "model_cases.json")) as f:
+            assert json.load(f) == json.loads(json.dumps(model_golden)), "model_cases.json is stale"
+        flat = {name + "." + k: a for name, d in small_arrays.items() for k, a in d.items()}
+        for fname, arrays in (("small_cases.npz", flat), ("model_heights.npz", model_arrays), ("real_000000.npz", dict(points=real0))):
+            with np.load(os.path.join(GOLDEN, fname)) as z:
+                assert sorted(z.files) == sorted(arrays), fname + ": key set differs"
+                for k in z.files:
+                    assert z[k].dtype == np.asarray(arrays[k]).dtype and z[k].tobytes() == np.asarray(arrays[k]).tobytes(), \
+                        "%s[%s] is stale" % (fname, k)
+        for cfgname in ("kitti", "camera"):
+            cfg = synth.make_cfg(cfgname, batch_size=len(calib_src[cfgname]))
+            sd0 = synth.make_state_dict(cfg, 0, None)
+            v, c, n = voxel_inputs(cfg, calib_src[cfgname])
+            with torch.no_grad():
+                vf = model_ref.pillar_feature_net(sd0, cfg, v, n, c)
+                canvas = model_ref.pillars_scatter(cfg, vf, c, cfg.batch_size)
+            from oracle.calibrate import calibrate
+            stats = calibrate(cfg, canvas.numpy(), 0)
+            with np.load(synth.bn_stats_path(cfgname)) as z:
+                for k in z.files:
+                    assert np.asarray(stats[k]).astype(z[k].dtype).tobytes() == z[k].tobytes(), "ckpt_%s_bn.npz[%s] is stale" % (cfgname, k)
+        print("[verify] the committed tests/golden/ fixtures are reproduced array for array")
     if args.write:
         os.makedirs(GOLDEN, exist_ok=True)
         with open(os.path.join(GOLDEN, "voxel_cases.json"), "w") as f:

@@ -146,7 +146,7 @@ def main():
     assert np.array_equal(mine, ref_counts)
     gold["eval__sem"], gold["eval__pred"], gold["eval__counts"], gold["eval__metrics"] = sem, pred.astype(np.int8), ref_counts, ref_metrics
     # ---- ground-truth rasterisation (8f row 3): the reference's numba lidar_to_img / lidar_to_heightmap as they are
-    from oracle import synth
+    from gndnet_b200 import synth
     cfgk = synth.make_cfg("kitti")
     gr = np.asarray(cfgk.grid_range)
     with np.load(os.path.join(GOLDEN, "real_000000.npz")) as z:

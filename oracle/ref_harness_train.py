@@ -20,7 +20,8 @@ def main():
     args = ap.parse_args()
     sys.path.insert(0, ROOT)
     import torch
-    from oracle import cpu_ops, model_ref, synth
+    from oracle import cpu_ops, model_ref
+    from gndnet_b200 import synth
     from oracle.ref_harness import import_reference
     from tests import cases
     _, refmodel, _ = import_reference()

@@ -5,7 +5,7 @@ import os
 
 import numpy as np
 
-from oracle import synth
+from gndnet_b200 import synth
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 

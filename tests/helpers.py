@@ -2,7 +2,8 @@
 import numpy as np
 import torch
 
-from oracle import cpu_ops, model_ref, synth
+from oracle import cpu_ops, model_ref
+from gndnet_b200 import synth
 
 
 def oracle_pillars(cfg, raws):

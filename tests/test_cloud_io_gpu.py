@@ -5,7 +5,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import cpu_ops, synth
+from oracle import cpu_ops
+from gndnet_b200 import synth
 from tests import cases, helpers
 from gndnet_b200 import ros_io
 

@@ -7,7 +7,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import cpu_ops, model_ref, synth
+from oracle import cpu_ops, model_ref
+from gndnet_b200 import synth
 from tests import cases, helpers
 
 pytestmark = pytest.mark.gpu

@@ -3,7 +3,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import cpu_ops, synth
+from oracle import cpu_ops
+from gndnet_b200 import synth
 from tests import cases
 
 pytestmark = pytest.mark.gpu

@@ -3,7 +3,8 @@ Prints max|dh| and label flip rate vs the fp32 oracle for fp16 / bf16 operands."
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch, torch.nn.functional as F
-from oracle import synth, cpu_ops, model_ref as mr
+from oracle import cpu_ops, model_ref as mr
+from gndnet_b200 import synth
 
 def fold(sd, name):
     p = "encoder_decoder." + name + ".cbr_unit."

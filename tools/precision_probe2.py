@@ -2,7 +2,8 @@
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch, torch.nn.functional as F
-from oracle import synth, cpu_ops, model_ref as mr
+from oracle import cpu_ops, model_ref as mr
+from gndnet_b200 import synth
 from tools.precision_probe import fold
 
 def split(t, scale=1.0):
