@@ -86,6 +86,9 @@ _SIGS = {
     "gnd_lidar_to_heightmap": (ctypes.c_int, [c_vp, c_i64, c_i32, ctypes.POINTER(c_d), c_d, c_i32, c_vp, c_sz, c_vp, c_vp]),
     "gnd_get_buffer": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.POINTER(c_vp), ctypes.POINTER(c_sz)]),
     "gnd_last_launch_count": (ctypes.c_int, [c_vp]),
+    "gnd_set_option": (ctypes.c_int, [c_vp, ctypes.c_char_p, c_i32]),
+    "gnd_conv_timing_begin": (ctypes.c_int, [c_vp, c_i32]),
+    "gnd_conv_timing_end": (ctypes.c_int, [c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_f), ctypes.POINTER(c_i32)]),
 }
 
 _lib = None

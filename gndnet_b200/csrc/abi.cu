@@ -88,8 +88,9 @@ int check_bound(gnd_ctx *ctx, int32_t batch, int64_t n_points, bool need_weights
     if (need_weights && !ctx->weights_loaded) return fail(GND_ERR_STATE, "gnd_load_weights has not been called");
     if (!ctx->ws) return fail(GND_ERR_STATE, "gnd_bind_workspace has not been called");
     if (batch < 1 || batch > ctx->B) return fail(GND_ERR_INVALID, "batch %d exceeds the bound batch %d", batch, ctx->B);
-    if (n_points >= 0 && n_points != ctx->N)
-        return fail(GND_ERR_INVALID, "n_points %lld differs from the bound n_points %lld", (long long)n_points, (long long)ctx->N);
+    // the workspace is bound to a CAPACITY (batch, n_points): any smaller batch / row count runs in it unchanged
+    if (n_points > ctx->N)
+        return fail(GND_ERR_INVALID, "n_points %lld exceeds the bound capacity %lld", (long long)n_points, (long long)ctx->N);
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e != cudaSuccess) return fail(GND_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
     return GND_OK;
@@ -107,7 +108,6 @@ extern "C" int gnd_workspace_bytes(const gnd_ctx *cctx, int32_t batch, int64_t n
     if (!cctx || !h_bytes) return fail(GND_ERR_INVALID, "null argument");
     gnd_ctx tmp = *cctx;     // sizes only; never touches device memory
     tmp.tmaps = nullptr;
-    tmp.hmaps = nullptr;
     tmp.h2maps = nullptr;
     int rc = vox_make_plan(&tmp.vparams, batch, n_points, &tmp.vplan);
     if (rc != GND_OK) return rc;
@@ -146,6 +146,54 @@ extern "C" int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t
 }
 
 extern "C" int gnd_last_launch_count(const gnd_ctx *ctx) { return ctx ? ctx->last_launches : 0; }
+
+extern "C" int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value) {
+    if (!ctx || !name) return fail(GND_ERR_INVALID, "null argument");
+    if (!strcmp(name, "conv_path")) {
+        if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "conv_path must be 0 (CTA-pair halo kernel) or 1 (single-CTA tap kernel)");
+        ctx->opt_conv_path = value;
+    } else if (!strcmp(name, "conv_geometry")) {
+        if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "conv_geometry must be 0 (auto), 1 (throughput) or 2 (small batch)");
+        ctx->opt_conv_geom = value;
+    } else {
+        return fail(GND_ERR_INVALID, "unknown option %s", name);
+    }
+    return GND_OK;
+}
+
+// ---- asynchronous per-convolution timing (bench.py's roofline: the kernel timed INSIDE a long run) -----------------
+static void timing_free(gnd_ctx *ctx) {
+    for (cudaEvent_t e : ctx->tim_events) cudaEventDestroy(e);
+    ctx->tim_events.clear();
+    ctx->tim_slots = ctx->tim_next = 0;
+}
+
+extern "C" int gnd_conv_timing_begin(gnd_ctx *ctx, int32_t slots) {
+    if (!ctx || slots < 1 || slots > 4096) return fail(GND_ERR_INVALID, "slots must be 1..4096");
+    GND_CUDA_CHECK(cudaSetDevice(ctx->device));
+    timing_free(ctx);
+    ctx->tim_events.resize((size_t)slots * 18);
+    for (cudaEvent_t &e : ctx->tim_events) GND_CUDA_CHECK(cudaEventCreate(&e));
+    ctx->tim_slots = slots;
+    return GND_OK;
+}
+
+extern "C" int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, int32_t *h_recorded) {
+    if (!ctx || !h_conv_ms || !h_segnet_ms || !h_recorded) return fail(GND_ERR_INVALID, "null argument");
+    GND_CUDA_CHECK(cudaSetDevice(ctx->device));
+    const int n = ctx->tim_next;
+    *h_recorded = n;
+    int rc = GND_OK;
+    for (int s = 0; s < n && rc == GND_OK; ++s) {
+        cudaEvent_t *ev = &ctx->tim_events[(size_t)s * 18];
+        cudaError_t e = cudaEventSynchronize(ev[17]);
+        for (int l = 0; l < 8 && e == cudaSuccess; ++l) e = cudaEventElapsedTime(&h_conv_ms[s * 8 + l], ev[2 * l], ev[2 * l + 1]);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&h_segnet_ms[s], ev[16], ev[17]);
+        if (e != cudaSuccess) rc = fail(GND_ERR_CUDA, "conv timing read-back: %s", cudaGetErrorString(e));
+    }
+    timing_free(ctx);
+    return rc;
+}
 
 extern "C" int gnd_voxelize(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
                             int64_t n_points, void *stream) {

@@ -5,7 +5,7 @@ cd "$(dirname "$0")"
 OUT=../libgndnet_b200.so
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden --fmad=true"
-SRCS="common.cu voxelize.cu segment.cu pfn.cu segnet.cu conv_tc.cu conv_halo.cu conv_halo2.cu weights.cu abi.cu cloud_io.cu raster.cu"
+SRCS="common.cu voxelize.cu segment.cu pfn.cu segnet.cu conv_tc.cu conv_halo2.cu weights.cu abi.cu cloud_io.cu raster.cu"
 mkdir -p build
 pids=()
 for s in $SRCS; do

@@ -32,6 +32,16 @@ inline void count_launch(int n = 1) { g_launches += n; }
         ::gnd::count_launch();                                                                    \
     } while (0)
 
+// Debug / tuning knobs from the environment, read ONCE per process (first use) -- never at launch time, so a
+// running service cannot change kernel geometry under a captured CUDA graph or between two threads' calls.
+//   GNDNET_DEBUG            print per-layer geometry when tensor maps are built
+//   GNDNET_VOX_SERIAL       force the one-ranking-warp voxel kernel        GNDNET_VOX_K / GNDNET_VOX_G  chunking overrides
+//   GNDNET_PFN_GSHIFT       pillar-encode work-unit size (log2 cells)       GNDNET_H2_SMALL_NT / GNDNET_H2_MINSB  conv ring
+struct Tuning {
+    int debug, vox_serial, vox_k, vox_g, pfn_gshift, h2_small_nt, h2_minsb;
+};
+const Tuning &tuning();
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // carve a caller-owned buffer

@@ -1,11 +1,27 @@
-// conv_halo2.cu -- the halo-reuse 3x3 convolution (see conv_halo.cu for the strip / shifted-view scheme) on a
-// CTA PAIR: tcgen05.mma.cta_group::2 with M = 256 (128 positions from each CTA), the weight tile split between
-// the two CTAs' shared memories.
+// conv_halo2.cu -- 3x3 convolution + folded BatchNorm + ReLU (conv2DBatchNormRelu, modules/segnet.py:11-44) as an
+// implicit GEMM on tcgen05 with the input HALO staged once per channel block, on a CTA PAIR
+// (tcgen05.mma.cta_group::2, M = 256 = 128 positions from each CTA, the weight tile split between the two CTAs'
+// shared memories).  The last block's epilogue also carries the regressor's channel contraction (segnet.py:131,140).
+//
+// Halo scheme.  A work item covers a run of consecutive positions of a vertical STRIP of the image:
+//   strip    = TW image columns plus one halo column on each side (padded width Wp = TW + 2)
+//   position q of a strip <-> (row q / Wp, padded column q % Wp); columns 0 and Wp-1 are halo: their outputs are
+//            computed and discarded (TW / Wp of the MMA rows are useful)
+//   half-item = MT tiles of 128 consecutive positions x NT output channels (MT * NT = 256 TMEM columns)
+// For one channel block ONE TMA box {kc channels, Wp columns, NR rows, 1 scan} of the NHWC activation lands in
+// shared memory (coordinates outside the image are zero-filled by the TMA unit: the conv's zero padding) as NR*Wp
+// rows of RB bytes with the RB-byte swizzle.  The A operand of tap (kh, kw) for tile t is then simply the 128 rows
+// that start (q0 - r_lo*Wp) + 128 t + kh*Wp + kw - 1 rows into the box: nine UMMA descriptors into the same bytes,
+// their start address moved by whole rows (the swizzle is a function of the absolute shared-memory address --
+// tools/umma_shift_probe.cu checks this on the hardware for both swizzle widths).  Activations come from L2 once
+// per channel block instead of nine times.  "split" layers (hi + lo fp16 planes, three products per K step:
+// DESIGN.md section 3) use 32-channel blocks (64-byte rows, SWIZZLE_64B) so two halo stages of both planes fit.
 //
 // Why a pair: an M128 x N128 x K16 MMA reads 4 KB of A and 4 KB of B from shared memory in its 64 clocks --
 // the whole 128 B/clk of the SM -- so every byte TMA writes into shared memory slows the tensor pipe down
-// (measured: 84-97 clk per MMA in conv_halo.cu against 64.6 in isolation).  With cta_group::2 each SM reads
-// its own 4 KB of A but only HALF of B (2 KB), 96 B/clk, and loads half as many weight bytes from L2.
+// (measured on the single-CTA predecessor of this kernel: 84-97 clk per MMA against 64.6 in isolation).  With
+// cta_group::2 each SM reads its own 4 KB of A but only HALF of B (2 KB), 96 B/clk, and loads half as many weight
+// bytes from L2.
 //
 // The two CTAs of a pair work on two INDEPENDENT half-items (any scan / strip / position range, same output-
 // channel tile): the only things the pair instruction shares are the weight tile and the operand OFFSETS, so
@@ -20,6 +36,10 @@
 //                     arrive.release.cluster per stage from the peer cost a cluster-scope fence each, ~1300 clk)
 //   a_empty / b_empty one per CTA, arrived by the leader's tcgen05.commit multicast to both CTAs
 //   t_full            one per CTA (commit multicast);  t_empty in the leader, count 8 (4 epilogue warps x 2 CTAs)
+//
+// Warp roles per CTA (256 threads, one persistent CTA per SM): warp 0 lane 0 halo (A) producer, warp 3 lane 0 weight (B)
+// producer, warp 1 lane 0 of the leader MMA issuer (two accumulator sets of 256 TMEM columns, ping-pong), warp 2 TMEM
+// allocator, warps 4-7 epilogue (tcgen05.ld -> bias + ReLU -> NHWC fp16 hi/lo stores, or the regressor head).
 #include "model.cuh"
 #include "tc_ptx.cuh"
 #include <stdlib.h>
@@ -461,7 +481,9 @@ static bool h2_geometry(int H, int W, int RB, int planes, int MT, int NT, int mi
 
 int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
     if (!ctx->h2maps) ctx->h2maps = new Halo2Maps();
-    const int small_nt = getenv("GNDNET_H2_SMALL_NT") ? atoi(getenv("GNDNET_H2_SMALL_NT")) : 64;
+    // once per build, not per launch: the opt-in limit covers every layer's ring (<= H2_RING_BUDGET + barriers + bias)
+    GND_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_halo2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    const int small_nt = tuning().h2_small_nt;
     for (int l2 = 0; l2 < 16; ++l2) {
         const int l = l2 >> 1;
         const bool small = (l2 & 1) != 0;
@@ -482,7 +504,7 @@ int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
         p.n_ntiles = L.cout / p.NT;
         const int planes = L.split ? 2 : 1;
         int NR = 0;
-        const int want_sb = getenv("GNDNET_H2_MINSB") ? atoi(getenv("GNDNET_H2_MINSB")) : 6;
+        const int want_sb = tuning().h2_minsb;
         if (!h2_geometry(in.H, in.W, p.RB, planes, p.MT, p.NT, want_sb, &p, &NR) &&
             !h2_geometry(in.H, in.W, p.RB, planes, p.MT, p.NT, 4, &p, &NR))
             continue;
@@ -509,7 +531,7 @@ int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]) {
         }
         hl.p = p;
         hl.usable = true;
-        if (getenv("GNDNET_DEBUG"))
+        if (tuning().debug)
             fprintf(stderr, "halo2 layer %d%s: %dx%d cin %d cout %d split %d | Wp %d strips %d tiles/strip %d MT %d NT %d NR %d SB %d row0 %d smem %zu\n",
                     l, small ? " (small-batch)" : "", in.H, in.W, L.cin, L.cout, L.split, p.Wp, p.strips, p.tiles_per_strip, p.MT, p.NT, NR, p.SB, p.row0, hl.smem);
     }
@@ -522,8 +544,7 @@ void halo2_free(gnd_ctx *ctx) {
 }
 
 bool halo2_usable(const gnd_ctx *ctx, int l) {
-    static const char *env = getenv("GNDNET_CONV");        // "tap" / "halo1" force the single-CTA kernels (A/B timing)
-    if (env && (env[0] == 't' || env[0] == 'h')) return false;
+    if (ctx->opt_conv_path == 1) return false;             // gnd_set_option("conv_path", 1): the single-CTA tap kernel
     return ctx->h2maps && ctx->h2maps->layer[l].usable;
 }
 
@@ -533,11 +554,10 @@ int halo2_conv_run(gnd_ctx *ctx, int l, const Act &out, int B, bool fuse_regress
     {
         const Halo2Layer &sm = ctx->h2maps->small[l];
         auto items = [&](const Halo2Params &q) { return ((B * q.strips * q.groups + 1) / 2) * q.n_ntiles; };
-        const char *force = getenv("GNDNET_H2_GEOM");             // "big" / "small": A/B timing and tests
+        const int force = ctx->opt_conv_geom;                      // gnd_set_option("conv_geometry"): 1 big, 2 small (tests)
         // (an N tile of 64 re-reads the halo once per N tile and runs the MMAs at the shared-memory limit: it pays only
         //  while the wide geometry leaves about half of the pairs idle -- measured at batch 1, 2 and 4)
-        if (sm.usable && ((items(pick->p) <= 40 && items(sm.p) > items(pick->p)) || (force && force[0] == 's'))
-            && !(force && force[0] == 'b'))
+        if (sm.usable && ((items(pick->p) <= 40 && items(sm.p) > items(pick->p)) || force == 2) && force != 1)
             pick = &sm;
     }
     const Halo2Layer &hl = *pick;
@@ -551,12 +571,11 @@ int halo2_conv_run(gnd_ctx *ctx, int l, const Act &out, int B, bool fuse_regress
     p.regpart = fuse_regressor ? ctx->regpart : nullptr;
     if (fuse_regressor && p.Cout != 64) return fail(GND_ERR_UNSUPPORTED, "regressor fusion needs a 64-channel last block");
     if (!fuse_regressor && !out.hi) return fail(GND_ERR_STATE, "layer %d: output activation missing", l);
-    GND_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_halo2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hl.smem));
     const int pairs = p.pair_items < 74 ? p.pair_items : 74;
     conv3x3_halo2_kernel<<<2 * pairs, H2_THREADS, hl.smem, st>>>(hl.a_hi, hl.a_lo, hl.b_hi, hl.b_lo, p);
     GND_LAUNCH_CHECK("conv3x3_halo2_kernel");
 #ifdef HALO_STATS
-    if (getenv("GNDNET_DEBUG")) {
+    if (tuning().debug) {
         unsigned long long h[8];
         cudaStreamSynchronize(st);
         cudaMemcpyFromSymbol(h, g_h2_stats, sizeof(h));

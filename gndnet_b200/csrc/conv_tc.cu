@@ -320,22 +320,19 @@ int tc_build_tensor_maps(gnd_ctx *ctx) {
     t.built = true;
     const Act *ins[8];
     for (int l = 0; l < 8; ++l) ins[l] = layer_input(ctx, l);
-    int rc = halo_build(ctx, ins);
-    if (rc != GND_OK) return rc;
+    GND_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     return halo2_build(ctx, ins);
 }
 
 void tc_free_tensor_maps(gnd_ctx *ctx) {
     delete ctx->tmaps;
     ctx->tmaps = nullptr;
-    halo_free(ctx);
     halo2_free(ctx);
 }
 
 int tc_conv_run(gnd_ctx *ctx, int l, const Act &in, const Act &out, int B, bool fuse_regressor, cudaStream_t st) {
     if (!ctx->tmaps || !ctx->tmaps->built) return fail(GND_ERR_STATE, "tensor maps not built (bind the workspace after loading weights)");
     if (halo2_usable(ctx, l)) return halo2_conv_run(ctx, l, out, B, fuse_regressor, st);
-    if (halo_usable(ctx, l)) return halo_conv_run(ctx, l, out, B, fuse_regressor, st);
     const TensorMaps &t = *ctx->tmaps;
     const ConvLayer &L = ctx->conv[l];
     ConvParams p;
@@ -363,7 +360,6 @@ int tc_conv_run(gnd_ctx *ctx, int l, const Act &in, const Act &out, int B, bool 
     if (fuse_regressor && p.NT != 64) return fail(GND_ERR_UNSUPPORTED, "regressor fusion needs a 64-channel last block");
     if (!fuse_regressor && !out.hi) return fail(GND_ERR_STATE, "layer %d: output activation missing", l);
     const size_t smem = (size_t)stages * p.stage_bytes + 1024 /*align*/ + (2 * TC_MAX_STAGES + 4) * 8 + 16 + 576 * 4;
-    GND_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = p.total_items < 148 ? p.total_items : 148;
     conv3x3_tc_kernel<<<grid, TC_THREADS, smem, st>>>(t.a_hi[l], t.a_lo[l], t.b_hi[l], t.b_lo[l], p);
     GND_LAUNCH_CHECK("conv3x3_tc_kernel");

@@ -35,7 +35,6 @@ struct ConvLayer {
 };
 
 struct TensorMaps;   // conv_tc.cu
-struct HaloMaps;     // conv_halo.cu
 struct Halo2Maps;    // conv_halo2.cu
 
 }  // namespace gnd
@@ -72,10 +71,18 @@ struct gnd_ctx {
     float *bn_ab = nullptr;         // [2][256] per-channel scale / shift of the current layer
     int32_t *pfn_ctr = nullptr; // [2] work-queue head + finished-CTA count of pfn_scatter_kernel (self-resetting)
     gnd::TensorMaps *tmaps = nullptr;
-    gnd::HaloMaps *hmaps = nullptr;
     gnd::Halo2Maps *h2maps = nullptr;
 
     int last_launches = 0;
+
+    // gnd_set_option
+    int opt_conv_path = 0;      // 0: CTA-pair halo kernel (conv_halo2.cu) where it fits, 1: single-CTA tap kernel (conv_tc.cu)
+    int opt_conv_geom = 0;      // 0: automatic, 1: throughput geometry, 2: small-batch geometry
+
+    // gnd_conv_timing_begin / _end: library-owned ring of CUDA events around the 8 convolution launches of every
+    // gnd_segnet / gnd_infer while armed (asynchronous: nothing is read back until _end)
+    std::vector<cudaEvent_t> tim_events;     // [slots][18]
+    int tim_slots = 0, tim_next = 0;
 };
 
 namespace gnd {
@@ -90,12 +97,7 @@ int segnet_run(gnd_ctx *ctx, int32_t batch, float *height, cudaStream_t st, cuda
 int tc_build_tensor_maps(gnd_ctx *ctx);
 void tc_free_tensor_maps(gnd_ctx *ctx);
 int tc_conv_run(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
-// conv_halo.cu (tcgen05 path, halo staged once per channel block)
-int halo_build(gnd_ctx *ctx, const Act *const inputs[8]);
-void halo_free(gnd_ctx *ctx);
-bool halo_usable(const gnd_ctx *ctx, int layer);
-int halo_conv_run(gnd_ctx *ctx, int layer, const Act &out, int batch, bool fuse_regressor, cudaStream_t st);
-// conv_halo2.cu (the same on a CTA pair, tcgen05 cta_group::2)
+// conv_halo2.cu (halo staged once per channel block, CTA pair, tcgen05 cta_group::2)
 int halo2_build(gnd_ctx *ctx, const Act *const inputs[8]);
 void halo2_free(gnd_ctx *ctx);
 bool halo2_usable(const gnd_ctx *ctx, int layer);

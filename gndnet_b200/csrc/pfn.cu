@@ -357,7 +357,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     const int64_t cells_all = (int64_t)batch * ctx->nx * ctx->ny;
     a.gshift = 3;
     while (a.gshift > 0 && (cells_all >> a.gshift) < 4 * 148 * 4 * PFN_WARPS) --a.gshift;
-    if (const char *e = getenv("GNDNET_PFN_GSHIFT")) a.gshift = atoi(e) < 0 ? 0 : (atoi(e) > 5 ? 5 : atoi(e));
+    if (tuning().pfn_gshift >= 0) a.gshift = tuning().pfn_gshift > 5 ? 5 : tuning().pfn_gshift;
     int64_t warps = (cells_all + (1 << a.gshift) - 1) >> a.gshift;
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically

@@ -53,7 +53,7 @@ __device__ __forceinline__ int seg_label(const SegArgs &a, int b, float *row, fl
 __global__ void __launch_bounds__(256) segment_kernel(const SegArgs a) {
     const int F = a.p.num_features;
     const int b = blockIdx.y;                              // one grid row per scan: no per-point division
-    const int n = a.counts ? a.counts[b] : (int)a.N;
+    const int n = a.counts ? max(0, min(a.counts[b], (int)a.N)) : (int)a.N;
     if (a.quad) {
         // four consecutive points per thread: the four 16-byte row loads are in flight together, the four int8
         // labels leave as one 4-byte store

@@ -425,6 +425,12 @@ static int conv_f32(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int 
 int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEvent_t *ev) {
     const bool tc = ctx->cfg.precision != GND_PREC_FP32;
     int rc;
+    bool ring = false;
+    if (!ev && ctx->tim_next < ctx->tim_slots) {          // armed by gnd_conv_timing_begin: next slot of the event ring
+        ev = &ctx->tim_events[(size_t)ctx->tim_next++ * 18];
+        ring = true;
+        cudaEventRecord(ev[16], st);
+    }
 #define CONV(l, in, out, fuse)                                                          \
     do {                                                                                \
         if (ev) cudaEventRecord(ev[2 * (l)], st);                                        \
@@ -460,6 +466,7 @@ int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEven
                                                                                           height, B, ctx->ny, ctx->nx);
         GND_LAUNCH_CHECK("regressor_f32_kernel");
     }
+    if (ring) cudaEventRecord(ev[17], st);
     return GND_OK;
 }
 

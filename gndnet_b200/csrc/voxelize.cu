@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) vox_rank_kernel(const VoxArgs a) {
     __shared__ int32_t s_cell[VOX_SUB];
     __shared__ uint16_t s_rank[VOX_SUB];
     const int b = blockIdx.x / a.K, k = blockIdx.x % a.K;
-    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
     const int start = k * a.T;
     const int end = min(start + a.T, n);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const
     uint2 *s_cnt = reinterpret_cast<uint2 *>(s_rt);                         // [cells] byte w = points warp w saw in this tile
     uint16_t *s_run = reinterpret_cast<uint16_t *>(s_cnt + a.cells);        // [cells] points seen in earlier tiles of the chunk
     const int b = blockIdx.x / a.K, k = blockIdx.x % a.K;
-    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
     const int start = k * a.T;
     const int end = min(start + a.T, n);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     __shared__ int s_cut, s_last;
     const int G = a.G;
     const int b = blockIdx.x / G, part = blockIdx.x - b * G, tid = threadIdx.x;
-    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
     const int nW = (n + 31) >> 5;
     const int32_t *first = a.ws.first + (int64_t)b * a.cells;
     int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
 // grid.y = (scan, chunk): no per-point divisions; grid.x strides over the chunk's points
 __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
     const int b = blockIdx.y / a.K, k = blockIdx.y - b * a.K;
-    const int n = a.counts ? min(a.counts[b], a.N) : a.N;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
     const int cstart = k * a.T, cend = min(cstart + a.T, a.N);
     const int cut = a.ws.cutoff[b];
     const int64_t base = (int64_t)b * a.N;
@@ -485,7 +485,7 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     if (cells > 100000) return fail(GND_ERR_UNSUPPORTED, "voxel grid of %lld cells > 100000 (shared-memory cell table)", (long long)cells);
     if (n_points > 1600000) return fail(GND_ERR_UNSUPPORTED, "%lld points per scan > 1600000 (shared-memory first-point bitmap)", (long long)n_points);
     plan->cells = (int32_t)cells;
-    plan->tiled = (cells <= VOX_RT_MAX_CELLS && !getenv("GNDNET_VOX_SERIAL")) ? 1 : 0;
+    plan->tiled = (cells <= VOX_RT_MAX_CELLS && !tuning().vox_serial) ? 1 : 0;
     const int64_t sub = plan->tiled ? VOX_RT_TILE : VOX_SUB;
     int64_t n = n_points < 1 ? 1 : n_points;
     int64_t kmin = (n + VOX_MAX_T - 1) / VOX_MAX_T;
@@ -500,7 +500,7 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
         if (kcap > 2 * 148) kcap = 2 * 148;
         if (k > kcap) k = kcap;
     }
-    if (const char *e = getenv("GNDNET_VOX_K")) { int v = atoi(e); if (v > 0 && v < k) k = v; }
+    if (tuning().vox_k > 0 && tuning().vox_k < k) k = tuning().vox_k;
     if (k > kmax) k = kmax;
     if (k < kmin) k = kmin;
     int64_t t = (n + k - 1) / k;
@@ -509,7 +509,7 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     plan->K = (int32_t)((n + t - 1) / t);
     {   // assign CTAs per scan: about two per SM over the batch, at most 16
         int g = (2 * 148) / batch;
-        if (const char *e = getenv("GNDNET_VOX_G")) g = atoi(e);
+        if (tuning().vox_g > 0) g = tuning().vox_g;
         plan->G = g < 1 ? 1 : (g > 16 ? 16 : g);
     }
     plan->rank_smem = plan->tiled ? (size_t)plan->cells * (sizeof(uint2) + sizeof(uint16_t)) : (size_t)plan->cells * sizeof(uint16_t);
@@ -556,12 +556,20 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     a.ws = ws; a.coors = coors; a.num_points = num_points; a.voxel_count = voxel_count;
     a.offsets = point_offsets; a.list = point_list; a.voxels = voxels; a.slot = point_slot;
 
-    GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    GND_CUDA_CHECK(cudaFuncSetAttribute(vox_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+    {   // opt-in shared-memory limits: once per device, not per call
+        static bool done[64] = {};
+        int dev = 0;
+        GND_CUDA_CHECK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !done[dev]) {
+            GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            GND_CUDA_CHECK(cudaFuncSetAttribute(vox_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+            GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            if (dev >= 0 && dev < 64) done[dev] = true;
+        }
+    }
     GND_CUDA_CHECK(cudaMemsetAsync(ws.first, 0x7f, ((size_t)batch * plan.cells + (size_t)batch) * sizeof(int32_t), stream));
     if (n_points > 0) {
         if (plan.tiled) {
-            GND_CUDA_CHECK(cudaFuncSetAttribute(vox_rank_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             vox_rank_tiles_kernel<<<batch * plan.K, VOX_RT_WARPS * 32, plan.rank_smem, stream>>>(a);
             GND_LAUNCH_CHECK("vox_rank_tiles_kernel");
         } else {

@@ -81,6 +81,7 @@ extern "C" void gnd_destroy(gnd_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     tc_free_tensor_maps(ctx);
+    for (cudaEvent_t e : ctx->tim_events) cudaEventDestroy(e);
     if (ctx->weight_blob) cudaFree(ctx->weight_blob);
     delete ctx;
 }

@@ -15,6 +15,7 @@ ros_node.py:227); the kernels fold it into the conv / linear weights at load tim
 height maps and per-point labels out, no dense ``voxels`` tensor and no host round trip.
 """
 import ctypes
+import threading
 import warnings
 
 import numpy as np
@@ -126,8 +127,12 @@ class GroundEstimatorNet(nn.Module):
         self._ws = None
         self._bound = None
         self._warned_train = False
-        self._tensors = None
         self.launches = 0
+        self._last_n = 0
+        # a gnd_ctx owns mutable device scratch: one stage call in flight per ctx (include/gndnet_b200.h, threading
+        # contract).  The reference runs inference on a daemon thread next to its callback thread (ros_node.py:51-60);
+        # calls from several threads on ONE model are serialised here.  ctypes releases the GIL inside the C calls.
+        self._lock = threading.RLock()
 
     # ------------------------------------------------------------------ context management
     def _config_struct(self):
@@ -160,10 +165,9 @@ class GroundEstimatorNet(nn.Module):
         return dev
 
     def _params_version(self):
-        # Parameter / buffer objects survive .cuda() and load_state_dict(); in-place updates bump _version
-        if self._tensors is None:
-            self._tensors = list(self.state_dict(keep_vars=True).values())
-        return tuple(t._version for t in self._tensors)
+        # identity AND in-place version of every parameter / buffer, rebuilt on every call (~60 entries): catches
+        # load_state_dict (in place), load_state_dict(assign=True), re-assigned Parameters and dtype / device moves
+        return tuple((id(t), t._version) for t in self.state_dict(keep_vars=True).values())
 
     def _ensure_ctx(self):
         dev = self._device()
@@ -177,7 +181,6 @@ class GroundEstimatorNet(nn.Module):
             self._ctx, self._ctx_device = handle, dev
             self._weights_version = None
             self._bound = None
-            self._tensors = None
         ver = self._params_version()
         if ver != self._weights_version:
             self._upload_weights()
@@ -202,9 +205,14 @@ class GroundEstimatorNet(nn.Module):
             _lib.check(L.gnd_load_weights(self._ctx, arr, len(sd)), "gnd_load_weights")
 
     def _ensure_workspace(self, batch, n_points):
+        """The workspace is bound to a CAPACITY (batch, n_points): smaller batches and shorter clouds reuse it as it is
+        (no synchronise, no reallocation, tensor maps and captured graphs stay valid); a larger request re-binds to the
+        element-wise maximum.  ``reserve()`` binds ahead of time."""
         L = _lib.lib()
-        if self._bound is not None and self._bound[0] >= batch and self._bound[1] == n_points:
+        if self._bound is not None and self._bound[0] >= batch and self._bound[1] >= n_points:
             return
+        if self._bound is not None:
+            batch, n_points = max(batch, self._bound[0]), max(n_points, self._bound[1])
         need = ctypes.c_size_t()
         _lib.check(L.gnd_workspace_bytes(self._ctx, batch, n_points, ctypes.byref(need)), "gnd_workspace_bytes")
         with torch.cuda.device(self._ctx_device):
@@ -216,6 +224,20 @@ class GroundEstimatorNet(nn.Module):
             _lib.check(L.gnd_bind_workspace(self._ctx, ctypes.c_void_p(ws.data_ptr() + off), need.value, batch, n_points),
                        "gnd_bind_workspace")
         self._bound = (batch, n_points)
+
+    def reserve(self, batch, n_points):
+        """Bind the workspace for up to ``batch`` scans of up to ``n_points`` points each, so that clouds of varying size
+        (ros_node.py:263 drops NaN rows per message; predict_ground.py loads files of different lengths) never re-bind."""
+        with self._lock:
+            self._ensure_ctx()
+            self._ensure_workspace(int(batch), int(n_points))
+
+    def set_option(self, name, value):
+        """gnd_set_option: "conv_path" (0 CTA-pair halo kernel, 1 single-CTA tap kernel), "conv_geometry" (0 auto, 1
+        throughput, 2 small-batch)."""
+        with self._lock:
+            self._ensure_ctx()
+            _lib.check(_lib.lib().gnd_set_option(self._ctx, name.encode(), int(value)), "gnd_set_option")
 
     def release(self):
         if self._ctx is not None:
@@ -250,6 +272,10 @@ class GroundEstimatorNet(nn.Module):
     # ------------------------------------------------------------------ reference API
     def forward(self, voxels, coors, num_points):
         """model.py:36-42 on the drop-in tensors."""
+        with self._lock:
+            return self._forward_locked(voxels, coors, num_points)
+
+    def _forward_locked(self, voxels, coors, num_points):
         self._check_mode()
         ctx = self._ensure_ctx()
         L = _lib.lib()
@@ -283,8 +309,13 @@ class GroundEstimatorNet(nn.Module):
         (predict_ground.py:112), voxelization, pillar encoding, scatter, segnet and the point labelling
         against ``cfg.grid_range`` (predict_ground.py:168) all run on the device, enqueued back to back.
         ``labels``: "int8", "float64" (the reference's dtype) or None.  ``out``: optional (height, labels)
-        tensors to write into.
+        tensors to write into.  ``counts``: optional int32 CUDA tensor [B], the number of valid rows of each scan
+        (rows beyond it are ignored and labelled -1); values are clamped to [0, N] on the device.
         """
+        with self._lock:
+            return self._infer_locked(points, threshold, counts, labels, out)
+
+    def _infer_locked(self, points, threshold, counts, labels, out):
         self._check_mode()
         ctx = self._ensure_ctx()
         L = _lib.lib()
@@ -294,8 +325,23 @@ class GroundEstimatorNet(nn.Module):
         if not (points.is_cuda and points.dtype == torch.float32 and points.is_contiguous()
                 and points.dim() == 3 and points.shape[2] == self.cfg.input_features):
             raise TypeError("points must be a contiguous float32 CUDA tensor [B, N, %d]" % self.cfg.input_features)
+        if points.device != self._ctx_device:
+            raise ValueError("points are on %s but the model is on %s" % (points.device, self._ctx_device))
         B, N, _ = points.shape
+        if counts is not None:
+            if not (torch.is_tensor(counts) and counts.dtype == torch.int32 and counts.is_contiguous()
+                    and counts.device == self._ctx_device and tuple(counts.shape) == (B,)):
+                raise TypeError("counts must be a contiguous int32 tensor of shape [%d] on %s" % (B, self._ctx_device))
+        if out is not None:
+            oh, ol = out
+            if not (oh.is_cuda and oh.device == self._ctx_device and oh.dtype == torch.float32 and oh.is_contiguous()
+                    and oh.numel() == B * self.ny * self.nx):
+                raise TypeError("out[0] must be a contiguous float32 tensor of %d x %d x %d on %s" % (B, self.ny, self.nx, self._ctx_device))
+            if ol is not None and not (ol.device == self._ctx_device and ol.dtype in (torch.int8, torch.float64)
+                                       and ol.is_contiguous() and ol.numel() == B * N):
+                raise TypeError("out[1] must be a contiguous int8 / float64 tensor of %d x %d on %s" % (B, N, self._ctx_device))
         self._ensure_workspace(B, N)
+        self._last_n = N
         dev = self._ctx_device
         with torch.cuda.device(dev):
             if out is not None:
@@ -323,6 +369,7 @@ class GroundEstimatorNet(nn.Module):
         ctx = self._ensure_ctx()
         B, N, _ = points.shape
         self._ensure_workspace(B, N)
+        self._last_n = N
         st = _lib.stream_ptr()
         l8 = labels if labels.dtype == torch.int8 else None
         l64 = labels if labels.dtype == torch.float64 else None
@@ -355,14 +402,34 @@ class GroundEstimatorNet(nn.Module):
         out["conv_kernel"] = "conv3x3_f32_kernel" if self.precision == "fp32" else "conv3x3_halo2_kernel"
         return out
 
+    def conv_timing_begin(self, slots):
+        """Arm gnd_conv_timing_begin: the next ``slots`` infer() / forward() calls record CUDA events around their eight
+        convolution launches, asynchronously (bench.py times the kernel inside a long back-to-back run this way)."""
+        with self._lock:
+            self._ensure_ctx()
+            _lib.check(_lib.lib().gnd_conv_timing_begin(self._ctx, int(slots)), "gnd_conv_timing_begin")
+            self._tim_slots = int(slots)
+
+    def conv_timing_end(self):
+        """-> (conv_ms [recorded, 8], segnet_ms [recorded]) float32 arrays; waits for the recorded events."""
+        with self._lock:
+            n = self._tim_slots
+            conv = (ctypes.c_float * (8 * n))()
+            seg = (ctypes.c_float * n)()
+            rec = ctypes.c_int32()
+            _lib.check(_lib.lib().gnd_conv_timing_end(self._ctx, conv, seg, ctypes.byref(rec)), "gnd_conv_timing_end")
+            r = rec.value
+            return (np.array(conv[:8 * r], dtype=np.float32).reshape(r, 8), np.array(seg[:r], dtype=np.float32))
+
     def pillars(self, batch):
         """Voxelizer outputs of the last infer() as tensors (views of the workspace)."""
         mv = int(getattr(self.cfg, "max_voxels", self.nx * self.ny * self.nz))
-        Bb, N = self._bound
+        Bb = self._bound[0]
+        N = self._last_n                     # row stride of the per-point buffers = the n_points of that call
         return dict(
             coors=self.buffer("coors", torch.int32, (Bb, mv, 3))[:batch],
             num_points=self.buffer("num_points", torch.int32, (Bb, mv))[:batch],
             voxel_count=self.buffer("voxel_count", torch.int32, (Bb,))[:batch],
             point_offsets=self.buffer("point_offsets", torch.int32, (Bb, mv + 1))[:batch],
-            point_list=self.buffer("point_list", torch.int32, (Bb, max(N, 1)))[:batch],
+            point_list=self.buffer("point_list", torch.int32)[:batch * max(N, 1)].view(batch, max(N, 1)),
         )

@@ -9,8 +9,13 @@ import torch
 
 
 class ScanStream:
-    def __init__(self, model, batch, n_points, depth=2, labels="int8", threshold=0.08):
+    """``split`` > 1 cuts every submitted batch into that many sub-batches, each with its own H2D copy -> infer -> D2H
+    chain: compute starts after the first sub-batch has landed instead of after the whole batch, which shortens the
+    pipeline's ramp-up and tail when the host link, not the GPU, is the bottleneck (several GPUs fed by one host)."""
+
+    def __init__(self, model, batch, n_points, depth=2, labels="int8", threshold=0.08, split=1):
         self.model, self.depth, self.threshold = model, depth, threshold
+        self.split = max(1, min(int(split), batch))
         dev = model._device()
         self.dev = dev
         F = model.cfg.input_features
@@ -27,34 +32,44 @@ class ScanStream:
                     h_labels=torch.empty((batch, n_points), dtype=ldt).pin_memory(),
                     ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event(), used=False))
         self.n = 0
+        model.reserve(batch, n_points)
         self.h2d_bytes = batch * n_points * F * 4
         self.d2h_bytes = batch * (model.ny * model.nx * 4 + n_points * (1 if ldt == torch.int8 else 8))
 
     def submit(self, host_points):
-        """Enqueue one batch of pinned host scans [B, N, F]; returns the slot holding its results."""
+        """Enqueue one batch of pinned host scans [b, N, F] (b <= the stream's batch); returns the slot holding its
+        results (rows [:b] of the slot's tensors)."""
         k = self.n % self.depth
         s = self.slots[k]
+        b = host_points.shape[0]
         cur = torch.cuda.current_stream(self.dev)
         ev = torch.cuda.Event()
         ev.record(cur)
         self.s_in.wait_event(ev)                       # ordered after the caller's earlier work
         if s["used"]:
             self.s_in.wait_event(s["ev_done"])         # the slot's previous scans have been consumed
-        with torch.cuda.stream(self.s_in):
-            s["points"].copy_(host_points, non_blocking=True)
-            s["ev_in"].record()
-        self.s_cmp.wait_event(s["ev_in"])
-        if s["used"]:
             self.s_cmp.wait_event(s["ev_out"])         # the slot's previous results have been read out
-        with torch.cuda.stream(self.s_cmp):
-            self.model.infer(s["points"], threshold=self.threshold, out=(s["height"], s["labels"]))
-            s["ev_done"].record()
-        self.s_out.wait_event(s["ev_done"])
-        with torch.cuda.stream(self.s_out):
-            s["h_height"].copy_(s["height"], non_blocking=True)
-            s["h_labels"].copy_(s["labels"], non_blocking=True)
-            s["ev_out"].record()
+        bounds = [(i * b) // self.split for i in range(self.split + 1)]
+        for lo, hi in zip(bounds[:-1], bounds[1:]):
+            if hi == lo:
+                continue
+            with torch.cuda.stream(self.s_in):
+                s["points"][lo:hi].copy_(host_points[lo:hi], non_blocking=True)
+                e_in = torch.cuda.Event()
+                e_in.record()
+            self.s_cmp.wait_event(e_in)
+            with torch.cuda.stream(self.s_cmp):
+                self.model.infer(s["points"][lo:hi], threshold=self.threshold, out=(s["height"][lo:hi], s["labels"][lo:hi]))
+                s["ev_done"].record()                   # after the last sub-batch: the slot's scans have been consumed
+                e_done = torch.cuda.Event()
+                e_done.record()
+            self.s_out.wait_event(e_done)
+            with torch.cuda.stream(self.s_out):
+                s["h_height"][lo:hi].copy_(s["height"][lo:hi], non_blocking=True)
+                s["h_labels"][lo:hi].copy_(s["labels"][lo:hi], non_blocking=True)
+                s["ev_out"].record()
         s["used"] = True
+        s["rows"] = b
         self.n += 1
         return k
 
@@ -69,7 +84,8 @@ class ScanStream:
         """Host tensors (height [B,ny,nx], labels [B,N]) of a submitted batch; blocks until they are there."""
         s = self.slots[slot]
         s["ev_out"].synchronize()
-        return s["h_height"], s["h_labels"]
+        b = s.get("rows", s["h_height"].shape[0])
+        return s["h_height"][:b], s["h_labels"][:b]
 
 
 class GraphedInfer:
@@ -81,24 +97,28 @@ class GraphedInfer:
     on the current stream), results appear in ``self.height`` / ``self.labels``.
     """
 
-    def __init__(self, model, batch, n_points, threshold=0.08, labels="int8"):
+    def __init__(self, model, batch, n_points, threshold=0.08, labels="int8", variable_n=False):
+        """``variable_n``: the graph also takes a device-side per-scan row count, so clouds of ANY size <= n_points
+        replay the same graph (``__call__`` takes [b, n, F] with n <= n_points and writes the counts)."""
         dev = model._device()
         self.model, self.dev = model, dev
+        self.n_points = int(n_points)
         F = model.cfg.input_features
         ldt = {"int8": torch.int8, "float64": torch.float64}[labels]
         with torch.cuda.device(dev), torch.no_grad():
             self.points = torch.zeros((batch, n_points, F), dtype=torch.float32, device=dev)
             self.height = torch.empty((batch, model.ny, model.nx), dtype=torch.float32, device=dev)
             self.labels = torch.empty((batch, n_points), dtype=ldt, device=dev)
+            self.counts = torch.full((batch,), n_points, dtype=torch.int32, device=dev) if variable_n else None
             side = torch.cuda.Stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):             # binds the workspace / uploads weights outside the capture
-                model.infer(self.points, threshold=threshold, out=(self.height, self.labels))
+                model.infer(self.points, threshold=threshold, counts=self.counts, out=(self.height, self.labels))
             torch.cuda.current_stream(dev).wait_stream(side)
             torch.cuda.synchronize(dev)
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
-                model.infer(self.points, threshold=threshold, out=(self.height, self.labels))
+                model.infer(self.points, threshold=threshold, counts=self.counts, out=(self.height, self.labels))
             self.launches = model.launches
             self._bound = model._bound
             self._wver = model._weights_version
@@ -107,7 +127,16 @@ class GraphedInfer:
         if self.model._bound != self._bound or self.model._params_version() != self._wver:
             raise RuntimeError("the model's workspace or weights changed after the graph was captured; build a new GraphedInfer")
         if points is not None:
-            self.points.copy_(points.reshape(self.points.shape), non_blocking=True)
+            if self.counts is not None:
+                if points.dim() == 2:
+                    points = points.unsqueeze(0)
+                b, n = points.shape[0], points.shape[1]
+                if b != self.points.shape[0] or n > self.n_points:
+                    raise ValueError("expected [%d, <=%d, F] scans" % (self.points.shape[0], self.n_points))
+                self.points[:, :n].copy_(points, non_blocking=True)
+                self.counts.fill_(n)
+            else:
+                self.points.copy_(points.reshape(self.points.shape), non_blocking=True)
         self.graph.replay()
         return self.height, self.labels
 

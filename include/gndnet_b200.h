@@ -174,7 +174,19 @@ typedef struct gnd_weight {
 GND_API int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n_entries);
 
 GND_API int gnd_workspace_bytes(const gnd_ctx *ctx, int32_t batch, int64_t n_points, size_t *h_bytes);
-/* Carves the caller's device buffer for (batch, n_points) and builds the TMA descriptors. */
+/* Carves the caller's device buffer for the CAPACITY (batch, n_points) and builds the TMA descriptors.  Every later
+ * stage call may pass any batch <= the bound batch and any n_points <= the bound n_points (the row count of the
+ * caller's [batch][n_points][F] buffer); clouds of different sizes -- ros_node.py's NaN-filtered clouds (:263),
+ * predict_ground.py's per-file sizes -- therefore run without re-binding.  Rows beyond counts[b] are ignored.
+ *
+ * Threading contract (the reference drives the path from a daemon thread while a callback thread segments the
+ * latest output, ros_node.py:51-60,96-126,270-274): a gnd_ctx owns mutable device scratch (work-queue counters,
+ * voxelizer tables, activations), so AT MOST ONE stage call per ctx may be in flight at a time -- serialise calls on
+ * one ctx (gndnet_b200.model takes a lock) and enqueue them on one stream, or use one ctx per thread / stream.
+ * The ctx-free entry points (gnd_points_to_voxel, gnd_segment_cloud, gnd_compact_obstacles, gnd_unpack_cloud, ...)
+ * keep all state in caller-owned buffers and are re-entrant.  Two ctxs may run concurrently on different streams:
+ * the convolution kernel takes a whole SM per CTA (all 512 TMEM columns), so kernels of different ctxs never
+ * co-reside on an SM and cannot starve each other's TMEM allocation. */
 GND_API int gnd_bind_workspace(gnd_ctx *ctx, void *workspace, size_t bytes, int32_t batch, int64_t n_points);
 
 GND_API int gnd_grid_shape(const gnd_ctx *ctx, int32_t *h_nz_ny_nx);
@@ -274,6 +286,16 @@ GND_API int gnd_lidar_to_heightmap(const float *points, int64_t n_points, int32_
 GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *bytes);
 /* Number of kernels the last gnd_* call on this ctx enqueued (bench.py's gpu_launches). */
 GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
+/* Per-ctx switches (tests, A/B timing; never read from the environment at launch time):
+ *   "conv_path"      0 = CTA-pair halo kernel where the shape fits (default), 1 = single-CTA tap kernel (the fallback)
+ *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel */
+GND_API int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value);
+/* Asynchronous per-convolution timing for bench.py's roofline: after _begin, each of the next `slots` gnd_segnet /
+ * gnd_infer calls records library-owned CUDA events around its 8 convolution launches (nothing is read back, the
+ * stream is not synchronised); _end waits for them, writes h_conv_ms[recorded][8] and h_segnet_ms[recorded] (device
+ * milliseconds) and frees the events. */
+GND_API int gnd_conv_timing_begin(gnd_ctx *ctx, int32_t slots);
+GND_API int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, int32_t *h_recorded);
 
 #ifdef __cplusplus
 }

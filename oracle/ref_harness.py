@@ -2,9 +2,9 @@
 
     python -m oracle.ref_harness [--write]
 
-1. imports /root/reference as the package ``gnd_net`` (symlink under the git-ignored
+1. imports the unmodified reference as the package ``gnd_net`` (verbatim copy under the git-ignored
    baseline/_ref/, stub modules for the ROS / plotting imports it cannot satisfy:
-   SURVEY.md section 8c),
+   SURVEY.md section 8c; baseline/refimpl.py),
 2. checks every stage of the restatement (oracle/gnd_oracle.c, oracle/model_ref.py) against the
    reference's own numba / torch code on the section 8d input set -- bit-exact for voxels, coors,
    num_points and labels, float-equal for the model stages,
@@ -27,28 +27,14 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
 def import_reference():
-    os.environ.setdefault("PYTHONDONTWRITEBYTECODE", "1")
+    """The unmodified reference as the package ``gnd_net`` (baseline/refimpl.py: verbatim copy under the git-ignored
+    baseline/_ref/, refreshed from /root/reference here)."""
     sys.dont_write_bytecode = True
-    link_dir = os.path.join(ROOT, "baseline", "_ref")
-    os.makedirs(link_dir, exist_ok=True)
-    link = os.path.join(link_dir, "gnd_net")
-    if not os.path.islink(link):
-        os.symlink(REF, link)
-    if link_dir not in sys.path:
-        sys.path.insert(0, link_dir)
-    for name in ["matplotlib", "matplotlib.pyplot", "shapely", "shapely.geometry",
-                 "gnd_net.ros2_numpy", "gnd_net.ros2_numpy.ros2_numpy"]:
-        if name not in sys.modules:
-            m = types.ModuleType(name)
-            if name == "shapely.geometry":
-                m.Polygon = object
-                m.Point = object
-            sys.modules[name] = m
-    import importlib
-    ops = importlib.import_module("gnd_net.utils.point_cloud_ops")
-    model = importlib.import_module("gnd_net.model")
-    utils = importlib.import_module("gnd_net.utils.utils")
-    return ops, model, utils
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    from baseline import refimpl
+    refimpl.install(force=True)
+    return refimpl.load()
 
 
 def ref_shift(points, h):

@@ -95,12 +95,55 @@ def flip_mask(model, st, tie_rel=2e-3, tie_abs=1e-4):
     return _dilate(m, 3), int(f1.sum()), int(f2.sum())      # through up1.conv1, up1.conv2, regressor
 
 
-def compare_heights(model, out, ref, st):
-    """-> (max |d| on unaffected pixels, fraction of pixels masked, max |d| overall, (#flips level 1, level 2))."""
+# Height bars of BASELINE.json's north_star and what the tests assert about them.  The bar itself (1e-3 m with fp32-class
+# arithmetic, 5e-3 m with 16-bit tensor-core operands) is asserted on every pixel outside the receptive field of an argmax
+# near-tie flip; ON TOP of that the unmasked map must meet the bar on all but MAX_FRAC_OVER of its pixels, the mask may
+# cover at most MAX_FRAC_MASKED of it, and the worst pixel anywhere is capped (a flip moves one near-tied activation by
+# one pixel: the output changes around it, it does not blow up).
+TOL = {"fp32": 1e-3, "split": 1e-3, "mixed": 5e-3}
+MAX_FRAC_OVER = {"fp32": 0.003, "split": 0.003, "mixed": 0.01}
+MAX_FRAC_MASKED = {"fp32": 0.04, "split": 0.04, "mixed": 0.08}
+MAX_OVERALL = 0.5          # metres
+
+
+def compare_heights(model, out, ref, st, precision=None):
+    """-> dict(stable_max: max |d| outside the flip mask, frac_masked, overall: max |d| anywhere, frac_over: fraction
+    of ALL pixels (no mask) over the precision's bar, median, flips: (#level 1, #level 2))."""
     B, _, H, W = st["out"].shape
     out = torch.as_tensor(out).reshape(B, H, W).cpu()
     ref = torch.as_tensor(ref).reshape(out.shape)
     d = (out - ref).abs()
     mask, n1, n2 = flip_mask(model, st)
     stable = d[~mask]
-    return float(stable.max()) if stable.numel() else 0.0, float(mask.float().mean()), float(d.max()), (n1, n2)
+    tol = TOL[precision or model.precision]
+    return dict(stable_max=float(stable.max()) if stable.numel() else 0.0, frac_masked=float(mask.float().mean()),
+                overall=float(d.max()), frac_over=float((d > tol).float().mean()), median=float(d.median()),
+                flips=(n1, n2), tol=tol)
+
+
+def assert_heights(rep, precision, st, what=""):
+    """The height-parity claim, measurable: see the constants above."""
+    line = ("%s %s: max|dh| outside flips=%.3g (bar %g)  over-bar pixels (unmasked map)=%.4f%%  masked=%.3f%%  "
+            "overall max=%.3g  median=%.2g  argmax flips=%s" %
+            (what, precision, rep["stable_max"], rep["tol"], 100 * rep["frac_over"], 100 * rep["frac_masked"],
+             rep["overall"], rep["median"], rep["flips"]))
+    print(line)
+    _record(dict(case=what, precision=precision, **rep))
+    assert rep["flips"][0] <= 1e-4 * st["p1"].numel() + 2 and rep["flips"][1] <= 1e-4 * st["p2"].numel() + 2, "too many argmax flips: " + line
+    assert rep["stable_max"] <= TOL[precision], line
+    assert rep["frac_over"] <= MAX_FRAC_OVER[precision], "too many pixels over the bar: " + line
+    assert rep["frac_masked"] <= MAX_FRAC_MASKED[precision], "flip mask too large: " + line
+    assert rep["overall"] <= MAX_OVERALL, line
+
+
+def _record(row):
+    """Append to gpurun_out/parity_report.jsonl (scratch; copied to profiles/ as the measured parity table)."""
+    import json
+    import os
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "parity_report.jsonl"), "a") as f:
+            f.write(json.dumps(row) + "\n")
+    except OSError:
+        pass
