@@ -76,6 +76,8 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
             names->push_back({"point_offsets", off, (size_t)B * (mv + 1) * 4});
             names->push_back({"point_list", list, (size_t)B * (size_t)(N < 1 ? 1 : N) * 4});
             names->push_back({"cell_voxel", ctx->vws.vid, (size_t)B * ctx->vplan.cells * 4});
+            names->push_back({"cell_offsets", ctx->vws.offc, (size_t)B * (ctx->vplan.cells + 1) * 4});
+            if (ctx->vws.sorted) names->push_back({"cell_points", ctx->vws.sorted, (size_t)B * (size_t)(N < 1 ? 1 : N) * 16});
         }
     }
     return c.bytes();
@@ -128,6 +130,8 @@ extern "C" int gnd_bind_workspace(gnd_ctx *ctx, void *workspace, size_t bytes, i
     ctx->ws = workspace; ctx->ws_bytes = bytes; ctx->B = batch; ctx->N = n_points;
     carve_all(ctx, batch, n_points, workspace, nullptr);
     GND_CUDA_CHECK(cudaMemset(ctx->pfn_ctr, 0, 4 * sizeof(int32_t)));
+    rc = vox_lean_init(ctx->vplan, ctx->vws, batch);
+    if (rc != GND_OK) { ctx->ws = nullptr; return rc; }
     if (ctx->cfg.precision != GND_PREC_FP32 && ctx->weights_loaded) {
         rc = tc_build_tensor_maps(ctx);
         if (rc != GND_OK) { ctx->ws = nullptr; return rc; }
@@ -152,6 +156,9 @@ extern "C" int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value) {
     if (!strcmp(name, "conv_path")) {
         if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "conv_path must be 0 (CTA-pair halo kernel) or 1 (single-CTA tap kernel)");
         ctx->opt_conv_path = value;
+    } else if (!strcmp(name, "vox_path")) {
+        if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "vox_path must be 0 (set-exact, fused path) or 1 (order-exact kernels)");
+        ctx->opt_vox_path = value;
     } else if (!strcmp(name, "conv_geometry")) {
         if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "conv_geometry must be 0 (auto), 1 (throughput) or 2 (small batch)");
         ctx->opt_conv_geom = value;
@@ -295,8 +302,14 @@ extern "C" int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *count
     if (rc != GND_OK) return rc;
     if (!height) return fail(GND_ERR_INVALID, "height is null");
     cudaStream_t st = (cudaStream_t)stream;
-    rc = vox_run(&ctx->vparams, ctx->vplan, ctx->vws, points, counts, batch, n_points, ctx->coors, ctx->num_points,
-                 ctx->voxel_count, ctx->offsets, ctx->list, nullptr, nullptr, st);
+    // the fused path needs per cell the SET of kept points, not the slot-ordered index lists: set-exact kernels
+    // (voxelize.cu); gnd_voxelize / gnd_points_to_voxel keep producing the lists with the order-exact ones
+    if (ctx->vplan.lean_ok && ctx->vws.lfirst && ctx->opt_vox_path == 0)
+        rc = vox_run_lean(&ctx->vparams, ctx->vplan, ctx->vws, points, counts, batch, n_points, ctx->coors, ctx->num_points,
+                          ctx->voxel_count, ctx->offsets, st);
+    else
+        rc = vox_run(&ctx->vparams, ctx->vplan, ctx->vws, points, counts, batch, n_points, ctx->coors, ctx->num_points,
+                     ctx->voxel_count, ctx->offsets, ctx->list, nullptr, nullptr, st);
     if (rc == GND_OK) rc = pfn_scatter_run(ctx, points, batch, n_points, st);
     if (rc == GND_OK) rc = segnet_run(ctx, batch, height, st);
     if (rc == GND_OK && (labels_i8 || labels_f64) && n_points > 0)

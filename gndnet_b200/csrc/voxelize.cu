@@ -452,6 +452,316 @@ __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
     }
 }
 
+// =============================================================================================================
+// Set-exact ("lean") voxelization for the fused pipeline (gnd_infer).
+//
+// What the rest of the path consumes is, per cell, the SET of its first max_points points in input order (the pillar
+// encoder's max and its fixed-point mean are order-independent inside a pillar), plus the bookkeeping the reference
+// returns: voxel ids in order of first appearance (coors), num_points, and the max_voxels break.  None of that needs the
+// rank of EVERY point inside its cell -- only, for the few over-full cells, the index of their max_points-th point:
+//   vl_count     every point: cell (16 bit) out, RED.ADD on the cell's count, RED.MIN on its first index (one atomic
+//                pair per run of equal cells inside a warp: LiDAR rings stay in a cell for many consecutive points)
+//   vl_cells     per cell: voxel id by popcount-prefix over the first-point bitmap, the break index, kept counts and
+//                the two CSR offset arrays (as vox_assign_kernel); over-full cells go on a compact list
+//   vl_collect   points of over-full cells (before the break) -> the cell's candidate list
+//   vl_select    one warp per over-full cell: the max_points-th smallest candidate index by a two-level radix select
+//                (1024-index buckets, then a 1024-bit bitmap) = the cell's keep threshold
+//   vl_fill      every point: kept iff its cell has a voxel, index < break and index <= threshold; slot by atomicAdd
+//                (any order); writes the cell-ordered float4 the pillar encoder reads
+// Same coors / num_points / voxel_count / offsets / kept sets as the order-exact kernels above (tests compare both paths
+// bit for bit, heights included); the per-voxel point index lists in slot order are produced only by the exact path
+// (gnd_voxelize, gnd_points_to_voxel).  All per-cell state is private to this path and restored by the kernels themselves
+// (vox_lean_init sets it once at bind time).
+constexpr int VL_NONE = 0x7f7f7f7f;
+constexpr int VL_SHIFT = 10;                    // select buckets of 1024 indices; N <= 1.6 M -> <= 1563 buckets
+
+__global__ void __launch_bounds__(256) vl_count_kernel(const VoxArgs a) {
+    const int b = blockIdx.y;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
+    const int64_t base = (int64_t)b * a.N;
+    uint16_t *cell16 = a.ws.lrank + base;
+    int32_t *first = a.ws.lfirst + (int64_t)b * a.cells;
+    int32_t *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+    const int lane = threadIdx.x & 31;
+    if (blockIdx.x == 0 && threadIdx.x < 4) a.ws.lstat[b * 4 + threadIdx.x] = 0;      // consumed by the kernels that follow
+    const int nround = (n + 31) & ~31;                                                   // whole warps stay converged
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < nround; i += gridDim.x * 256) {
+        int c = -1;
+        if (i < n) {
+            c = point_cell(a, a.points + (base + i) * a.F);
+            cell16[i] = (uint16_t)(c < 0 ? 0xffff : c);
+        }
+        // runs of equal cells among the 32 consecutive points of the warp: the run's first lane speaks for all of it
+        const int prev = __shfl_up_sync(0xffffffffu, c, 1);
+        const bool head = (lane == 0) || (c != prev);
+        const unsigned heads = __ballot_sync(0xffffffffu, head);
+        if (head && c >= 0) {
+            const unsigned later = heads & ~((2u << lane) - 1u);
+            const int len = (later ? __ffs(later) - 1 : 32) - lane;
+            atomicAdd(cnt + c, len);
+            atomicMin(first + c, i);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
+    extern __shared__ uint32_t s_bm[];             // bit i set <=> point i is the first point of a cell
+    __shared__ int s_tpre[1024];
+    __shared__ int s_warp[33];
+    __shared__ int s_cut, s_last;
+    const int G = a.G;
+    const int b = blockIdx.x / G, part = blockIdx.x - b * G, tid = threadIdx.x;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
+    const int nW = (n + 31) >> 5;
+    int32_t *first = a.ws.lfirst + (int64_t)b * a.cells;
+    int32_t *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+    int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
+    int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
+    int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
+    int32_t *hot = a.ws.lhot + (int64_t)b * a.cells;
+    int32_t *stat = a.ws.lstat + b * 4;
+    int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
+    int32_t *coors = a.coors + (int64_t)b * a.max_voxels * 3;
+    int32_t *num = a.num_points + (int64_t)b * a.max_voxels;
+    int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
+    int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
+
+    for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
+    if (tid == 0) s_cut = INT_MAX;
+    __syncthreads();
+    for (int c = tid; c < a.cells; c += 1024) {
+        const int f = __ldcg(first + c);
+        if (f < n) atomicOr(&s_bm[f >> 5], 1u << (f & 31));
+    }
+    __syncthreads();
+    const int seg = (nW + 1023) / 1024;
+    int local = 0;
+    for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) local += __popc(s_bm[w]);
+    int n_occ;
+    const int pre = block_exclusive_scan(local, s_warp, &n_occ);
+    s_tpre[tid] = pre;
+    const int M = min(n_occ, a.max_voxels);
+    // break index (point_cloud_ops.py:44-45): the first point of the cell whose rank is max_voxels
+    if (n_occ > a.max_voxels && pre <= a.max_voxels && a.max_voxels < pre + local) {
+        int r = pre;
+        for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) {
+            uint32_t m = s_bm[w];
+            const int pc = __popc(m);
+            if (r + pc > a.max_voxels) {
+                for (int k = a.max_voxels - r; k > 0; --k) m &= m - 1;
+                s_cut = w * 32 + __ffs(m) - 1;
+                break;
+            }
+            r += pc;
+        }
+    }
+    __syncthreads();
+    const int cut = s_cut;
+    const bool overflow = cut < n;
+
+    const int per = (a.cells + G - 1) / G;
+    const int c_lo = min(part * per, a.cells), c_hi = min(c_lo + per, a.cells);
+    const int nx = a.grid[0], ny = a.grid[1];
+    // pass 1 over the slice: voxel ids and coors; with the break, counts are re-taken over the points before it
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        const int f = __ldcg(first + c);
+        int v = -1;
+        if (f < n) {
+            const int w = f >> 5, t = w / seg;
+            int r = s_tpre[t];
+            for (int w2 = t * seg; w2 < w; ++w2) r += __popc(s_bm[w2]);
+            r += __popc(s_bm[w] & ((1u << (f & 31)) - 1u));
+            if (r < a.max_voxels) {
+                v = r;
+                const int cx = c % nx, cyz = c / nx;
+                const int cy = (a.grid[2] == 1) ? cyz : cyz % ny, cz = (a.grid[2] == 1) ? 0 : cyz / ny;
+                if (a.reverse) { coors[v * 3 + 0] = cz; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cx; }
+                else           { coors[v * 3 + 0] = cx; coors[v * 3 + 1] = cy; coors[v * 3 + 2] = cz; }
+            }
+        }
+        vid[c] = v;
+        fill[c] = 0;
+    }
+    if (overflow) {
+        __syncthreads();
+        const uint16_t *cell16 = a.ws.lrank + (int64_t)b * a.N;
+        for (int j = tid; j < cut; j += 1024) {
+            const int c = cell16[j];
+            if (c >= c_lo && c < c_hi && vid[c] >= 0) atomicAdd(fill + c, 1);
+        }
+        __syncthreads();
+    }
+    // pass 2: kept counts, over-full cells
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        const int v = vid[c];
+        int have = __ldcg(cnt + c);
+        cnt[c] = 0;                                       // restored for the next call
+        if (overflow) { have = fill[c]; fill[c] = 0; }
+        if (v < 0) have = 0;
+        const int kept = min(have, a.max_points);
+        if (v >= 0) num[v] = kept;
+        offc[c] = kept;
+        if (have > a.max_points) {
+            hot[atomicAdd(stat + 0, 1)] = c;
+            hoff[c] = atomicAdd(stat + 1, have);
+            thr[c] = -1;                                  // set by vl_select_kernel
+        } else {
+            hoff[c] = -1;
+            thr[c] = INT_MAX;
+        }
+    }
+    if (G > 1) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            s_last = (atomicAdd(stat + 2, 1) == G - 1);
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) return;
+    } else {
+        __syncthreads();
+    }
+    // every CTA of the scan has read `first`: restore it, then the CSR offsets (cell order / voxel order)
+    for (int c = tid; c < a.cells; c += 1024) first[c] = VL_NONE;
+    {
+        const int cpt = (a.cells + 1023) / 1024;
+        const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
+        int lsum = 0;
+        for (int c = cbeg; c < cend; ++c) lsum += __ldcg(offc + c);
+        int S;
+        int run = block_exclusive_scan(lsum, s_warp, &S);
+        for (int c = cbeg; c < cend; ++c) { const int k = __ldcg(offc + c); offc[c] = run; run += k; }
+        if (tid == 0) offc[a.cells] = S;
+        const int vpt = (M + 1023) / 1024;
+        const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
+        lsum = 0;
+        for (int v = vbeg; v < vend; ++v) lsum += __ldcg(num + v);
+        int S2;
+        run = block_exclusive_scan(lsum, s_warp, &S2);
+        for (int v = vbeg; v < vend; ++v) { off[v] = run; run += __ldcg(num + v); }
+        if (tid == 0) {
+            off[M] = S;
+            a.voxel_count[b] = M;
+            a.ws.cutoff[b] = cut;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
+    const int b = blockIdx.y;
+    if (a.ws.lstat[b * 4] == 0) return;                   // no over-full cell in this scan
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
+    const int lim = min(n, a.ws.cutoff[b]);
+    const int64_t base = (int64_t)b * a.N;
+    const uint16_t *cell16 = a.ws.lrank + base;
+    const int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
+    int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
+    int32_t *cand = a.ws.cell + base;                     // the exact path's cell buffer doubles as the candidate lists
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < lim; i += gridDim.x * 256) {
+        const int c = cell16[i];
+        if (c == 0xffff) continue;
+        const int o = __ldg(hoff + c);
+        if (o >= 0) cand[o + atomicAdd(fill + c, 1)] = i;
+    }
+}
+
+constexpr int VL_SEL_WARPS = 8;
+
+__global__ void __launch_bounds__(VL_SEL_WARPS * 32) vl_select_kernel(const VoxArgs a, int nbuckets) {
+    extern __shared__ uint32_t s_sel[];                   // per warp: [nbuckets] bucket counts + [32] bitmap words
+    const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nh = a.ws.lstat[b * 4];
+    uint32_t *hist = s_sel + (size_t)warp * (nbuckets + 32);
+    uint32_t *bits = hist + nbuckets;
+    const int32_t *hot = a.ws.lhot + (int64_t)b * a.cells;
+    const int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
+    int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
+    int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
+    const int32_t *cand_all = a.ws.cell + (int64_t)b * a.N;
+    for (int j = blockIdx.x * VL_SEL_WARPS + warp; j < nh; j += gridDim.x * VL_SEL_WARPS) {
+        const int c = hot[j];
+        const int m = fill[c];                            // candidates collected (> max_points)
+        const int32_t *cand = cand_all + hoff[c];
+        if (m <= a.max_points) {                          // cannot happen (the cell would not be on the list); stay safe
+            if (lane == 0) { thr[c] = INT_MAX; fill[c] = 0; }
+            continue;
+        }
+        for (int k = lane; k < nbuckets; k += 32) hist[k] = 0;
+        bits[lane] = 0;
+        __syncwarp();
+        for (int k = lane; k < m; k += 32) atomicAdd(&hist[cand[k] >> VL_SHIFT], 1u);
+        __syncwarp();
+        // the bucket that holds the max_points-th smallest index
+        const int per = (nbuckets + 31) / 32;
+        const int k0 = min(lane * per, nbuckets), k1 = min(k0 + per, nbuckets);
+        int mine = 0;
+        for (int k = k0; k < k1; ++k) mine += (int)hist[k];
+        const int incl = warp_inclusive_scan(mine);
+        const int before_lane = incl - mine;
+        const bool holds = before_lane < a.max_points && a.max_points <= incl;
+        int bstar = 0, before = 0;
+        if (holds) {
+            int run = before_lane;
+            for (int k = k0; k < k1; ++k) {
+                if (run + (int)hist[k] >= a.max_points) { bstar = k; before = run; break; }
+                run += (int)hist[k];
+            }
+        }
+        const unsigned who = __ballot_sync(0xffffffffu, holds);
+        const int src = __ffs(who) - 1;
+        bstar = __shfl_sync(0xffffffffu, bstar, src);
+        before = __shfl_sync(0xffffffffu, before, src);
+        for (int k = lane; k < m; k += 32) {
+            const int i = cand[k];
+            if ((i >> VL_SHIFT) == bstar) atomicOr(&bits[(i >> 5) & 31], 1u << (i & 31));
+        }
+        __syncwarp();
+        // the r-th set bit (1-based) of the 1024-bit map, r = max_points - before
+        const int r = a.max_points - before;
+        const uint32_t word = bits[lane];
+        const int pc = __popc(word);
+        const int pincl = warp_inclusive_scan(pc);
+        const bool here = (pincl - pc) < r && r <= pincl;
+        int pos = 0;
+        if (here) {
+            uint32_t w = word;
+            for (int k = r - (pincl - pc) - 1; k > 0; --k) w &= w - 1;
+            pos = lane * 32 + __ffs(w) - 1;
+        }
+        const unsigned who2 = __ballot_sync(0xffffffffu, here);
+        pos = __shfl_sync(0xffffffffu, pos, __ffs(who2) - 1);
+        if (lane == 0) {
+            thr[c] = (bstar << VL_SHIFT) + pos;
+            fill[c] = 0;                                  // becomes the slot counter of vl_fill_kernel
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) vl_fill_kernel(const VoxArgs a) {
+    const int b = blockIdx.y;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
+    const int lim = min(n, a.ws.cutoff[b]);
+    const int64_t base = (int64_t)b * a.N;
+    const uint16_t *cell16 = a.ws.lrank + base;
+    const int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
+    const int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
+    const int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
+    int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < lim; i += gridDim.x * 256) {
+        const int c = cell16[i];
+        if (c == 0xffff) continue;
+        if (__ldg(vid + c) < 0 || i > __ldg(thr + c)) continue;
+        const float *src = a.points + (base + i) * a.F;
+        float4 pt;
+        if (a.vec4) pt = __ldg(reinterpret_cast<const float4 *>(src));
+        else pt = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), a.F > 3 ? __ldg(src + 3) : 0.0f);
+        if (a.apply_shift) pt.z = __fadd_rn(pt.z, a.z_shift);
+        a.ws.sorted[base + __ldg(offc + c) + atomicAdd(fill + c, 1)] = pt;
+    }
+}
+
 // predict_ground.py:104-107: cloud[:, :4] += float32([0, 0, h, 0]) (so -0.0 becomes +0.0 in every column)
 __global__ void shift_cloud_kernel(float *points, int64_t rows, int F, float h) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -514,6 +824,7 @@ int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, Vo
     }
     plan->rank_smem = plan->tiled ? (size_t)plan->cells * (sizeof(uint2) + sizeof(uint16_t)) : (size_t)plan->cells * sizeof(uint16_t);
     plan->assign_smem = (size_t)((n_points + 31) / 32 + 1) * sizeof(uint32_t);
+    plan->lean_ok = (cells <= 65534) ? 1 : 0;
     return GND_OK;
 }
 
@@ -530,18 +841,21 @@ size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws,
     w.cutoff = c.take<int32_t>((size_t)batch);
     w.offc = c.take<int32_t>((size_t)batch * (plan.cells + 1));
     w.sorted = with_sorted ? c.take<float4>(bn) : nullptr;
+    const bool lean = with_sorted && plan.lean_ok;
+    const size_t bc = (size_t)batch * plan.cells;
+    w.lfirst = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lcnt = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lfill = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lthr = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lhoff = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lhot = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lstat = lean ? c.take<int32_t>((size_t)batch * 4) : nullptr;
     if (out) *out = w;
     return c.bytes();
 }
 
-int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
-            const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
-            int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,
-            int32_t *point_slot, cudaStream_t stream) {
-    if (!coors || !num_points || !voxel_count || !point_offsets || !point_list)
-        return fail(GND_ERR_INVALID, "voxelizer output pointer is null");
-    if (n_points > 0 && !points) return fail(GND_ERR_INVALID, "points is null");
-    VoxArgs a;
+static void fill_args(VoxArgs &a, const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+                      const int32_t *counts, int32_t batch, int64_t n_points) {
     a.points = points; a.counts = counts; a.B = batch; a.N = (int32_t)n_points; a.F = p->num_features;
     a.vec4 = (p->num_features == 4 && ((uintptr_t)points % 16) == 0) ? 1 : 0;
     for (int j = 0; j < 3; ++j) {
@@ -553,6 +867,75 @@ int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, con
     a.cells = plan.cells; a.K = plan.K; a.T = plan.T; a.G = plan.G;
     a.apply_shift = p->apply_z_shift; a.z_shift = p->z_shift;
     a.max_points = p->max_points; a.max_voxels = p->max_voxels; a.reverse = p->reverse_index;
+    a.ws = ws;
+}
+
+static int vl_attrs() {
+    static bool done[64] = {};
+    int dev = 0;
+    GND_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        if (dev >= 0 && dev < 64) done[dev] = true;
+    }
+    return GND_OK;
+}
+
+int vox_lean_init(const VoxPlan &plan, const VoxWs &ws, int32_t batch) {      // set-up time (gnd_bind_workspace): synchronous
+    if (!ws.lfirst) return GND_OK;
+    const size_t bc = (size_t)batch * plan.cells;
+    GND_CUDA_CHECK(cudaMemset(ws.lfirst, 0x7f, bc * sizeof(int32_t)));
+    GND_CUDA_CHECK(cudaMemset(ws.lcnt, 0, bc * sizeof(int32_t)));
+    GND_CUDA_CHECK(cudaMemset(ws.lfill, 0, bc * sizeof(int32_t)));
+    GND_CUDA_CHECK(cudaMemset(ws.lstat, 0, (size_t)batch * 4 * sizeof(int32_t)));
+    return GND_OK;
+}
+
+int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+                 const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
+                 int32_t *voxel_count, int32_t *point_offsets, cudaStream_t stream) {
+    if (!plan.lean_ok || !ws.lfirst || !ws.sorted) return fail(GND_ERR_STATE, "workspace has no set-exact voxelizer state");
+    if (!coors || !num_points || !voxel_count || !point_offsets) return fail(GND_ERR_INVALID, "voxelizer output pointer is null");
+    if (n_points > 0 && !points) return fail(GND_ERR_INVALID, "points is null");
+    VoxArgs a;
+    fill_args(a, p, plan, ws, points, counts, batch, n_points);
+    a.coors = coors; a.num_points = num_points; a.voxel_count = voxel_count; a.offsets = point_offsets;
+    a.list = nullptr; a.voxels = nullptr; a.slot = nullptr;
+    int rc = vl_attrs();
+    if (rc != GND_OK) return rc;
+    // point-parallel kernels: about eight CTAs per SM over the whole batch
+    int gx = (int)((n_points + 255) / 256);
+    const int want = (148 * 8 + batch - 1) / batch;
+    if (gx > want) gx = want;
+    if (gx < 1) gx = 1;
+    vl_count_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
+    GND_LAUNCH_CHECK("vl_count_kernel");
+    vl_cells_kernel<<<batch * plan.G, 1024, plan.assign_smem, stream>>>(a);
+    GND_LAUNCH_CHECK("vl_cells_kernel");
+    if (n_points > 0) {
+        vl_collect_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
+        GND_LAUNCH_CHECK("vl_collect_kernel");
+        const int nbuckets = (int)(n_points >> VL_SHIFT) + 1;
+        int sx = (148 * 4 + batch - 1) / batch;
+        if (sx < 1) sx = 1;
+        vl_select_kernel<<<dim3(sx, batch), VL_SEL_WARPS * 32, (size_t)VL_SEL_WARPS * (nbuckets + 32) * sizeof(uint32_t), stream>>>(a, nbuckets);
+        GND_LAUNCH_CHECK("vl_select_kernel");
+        vl_fill_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
+        GND_LAUNCH_CHECK("vl_fill_kernel");
+    }
+    return GND_OK;
+}
+
+int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+            const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
+            int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,
+            int32_t *point_slot, cudaStream_t stream) {
+    if (!coors || !num_points || !voxel_count || !point_offsets || !point_list)
+        return fail(GND_ERR_INVALID, "voxelizer output pointer is null");
+    if (n_points > 0 && !points) return fail(GND_ERR_INVALID, "points is null");
+    VoxArgs a;
+    fill_args(a, p, plan, ws, points, counts, batch, n_points);
     a.ws = ws; a.coors = coors; a.num_points = num_points; a.voxel_count = voxel_count;
     a.offsets = point_offsets; a.list = point_list; a.voxels = voxels; a.slot = point_slot;
 

@@ -22,6 +22,7 @@ struct VoxPlan {
     int32_t tiled;       // 1: vox_rank_tiles_kernel (grids <= VOX_RT_MAX_CELLS cells), 0: vox_rank_kernel
     size_t rank_smem;    // dynamic smem of the rank kernel
     size_t assign_smem;  // dynamic smem of the assign kernel
+    int32_t lean_ok;     // the set-exact path applies (cells fit 16 bits)
 };
 
 // scratch carved from the caller's workspace
@@ -35,10 +36,25 @@ struct VoxWs {
     int32_t *cutoff;     // [B]         first dropped index when max_voxels overflows, else INT_MAX
     int32_t *offc;       // [B][cells+1] CSR offsets of the kept points in CELL order (pillar-encode input)
     float4 *sorted;      // [B][N]      kept points (x, y, z [+shift], r) grouped by cell, slot order inside; may be null
+    // ---- set-exact ("lean") path of the fused pipeline: private, self-resetting state (see voxelize.cu) ----
+    int32_t *lfirst;     // [B][cells]  index of the cell's first in-range point (INT_MAX-like between calls)
+    int32_t *lcnt;       // [B][cells]  in-range points of the cell (0 between calls)
+    int32_t *lfill;      // [B][cells]  slot counter / collected-candidate counter
+    int32_t *lthr;       // [B][cells]  largest kept point index of the cell (INT_MAX: keep all)
+    int32_t *lhoff;      // [B][cells]  offset of the cell's candidate list in hot_idx, -1 if the cell is not over-full
+    int32_t *lhot;       // [B][cells]  compact list of over-full cells
+    int32_t *lstat;      // [B][4]      over-full cells, total candidates, cells CTAs finished, spare
 };
 
 int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, VoxPlan *plan);
 size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out, bool with_sorted = false);
+// Fused pipeline only: the same voxel ids / coors / num_points / voxel_count / offsets and, per cell, the same SET of kept
+// points (cell-ordered `sorted` + CSR `offc`) as vox_run, without ranking every point in input order; the per-voxel point
+// index lists (`point_list`) are NOT produced.
+int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
+                 const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
+                 int32_t *voxel_count, int32_t *point_offsets, cudaStream_t stream);
+int vox_lean_init(const VoxPlan &plan, const VoxWs &ws, int32_t batch);
 int vox_run(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
             const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
             int32_t *voxel_count, int32_t *point_offsets, int32_t *point_list, float *voxels,

@@ -129,6 +129,7 @@ class GroundEstimatorNet(nn.Module):
         self._warned_train = False
         self.launches = 0
         self._last_n = 0
+        self._slots = None
         # a gnd_ctx owns mutable device scratch: one stage call in flight per ctx (include/gndnet_b200.h, threading
         # contract).  The reference runs inference on a daemon thread next to its callback thread (ros_node.py:51-60);
         # calls from several threads on ONE model are serialised here.  ctypes releases the GIL inside the C calls.
@@ -165,11 +166,18 @@ class GroundEstimatorNet(nn.Module):
         return dev
 
     def _params_version(self):
-        # identity AND in-place version of every parameter / buffer, rebuilt on every call (~60 entries): catches
-        # load_state_dict (in place), load_state_dict(assign=True), re-assigned Parameters and dtype / device moves
-        return tuple((id(t), t._version) for t in self.state_dict(keep_vars=True).values())
+        # identity AND in-place version of every parameter / buffer, looked up afresh on every call through the owning
+        # modules' dicts (the module tree is fixed, the tensor objects are not): catches load_state_dict (in place),
+        # load_state_dict(assign=True), re-assigned Parameters and dtype / device moves.  ~60 dict lookups, a few
+        # microseconds -- it sits on the batch-1 latency path (state_dict() here cost ~75 us per call).
+        if self._slots is None:
+            self._slots = [(d, n) for m in self.modules() for d in (m._parameters, m._buffers) for n in d]
+        return tuple((id(t), t._version) for t in (d[n] for d, n in self._slots) if t is not None)
 
-    def _ensure_ctx(self):
+    def _ensure_ctx(self, defer_version_check=False):
+        """``defer_version_check``: the latency path (infer) compares the parameter versions AFTER its launches are
+        enqueued -- the ~20 us walk then overlaps the device work instead of delaying the first kernel -- and re-runs
+        in the rare case they changed (_weights_stale)."""
         dev = self._device()
         L = _lib.lib()
         if self._ctx is None or self._ctx_device != dev:
@@ -181,11 +189,22 @@ class GroundEstimatorNet(nn.Module):
             self._ctx, self._ctx_device = handle, dev
             self._weights_version = None
             self._bound = None
+        if defer_version_check and self._weights_version is not None:
+            return self._ctx
         ver = self._params_version()
         if ver != self._weights_version:
             self._upload_weights()
             self._weights_version = ver
         return self._ctx
+
+    def _weights_stale(self):
+        """True (after re-uploading) if a parameter changed since the last upload."""
+        ver = self._params_version()
+        if ver == self._weights_version:
+            return False
+        self._upload_weights()
+        self._weights_version = ver
+        return True
 
     def _upload_weights(self):
         """gnd_load_weights: the C side of load_state_dict (BatchNorm folding + repack)."""
@@ -317,7 +336,7 @@ class GroundEstimatorNet(nn.Module):
 
     def _infer_locked(self, points, threshold, counts, labels, out):
         self._check_mode()
-        ctx = self._ensure_ctx()
+        ctx = self._ensure_ctx(defer_version_check=True)
         L = _lib.lib()
         single = points.dim() == 2
         if single:
@@ -355,8 +374,11 @@ class GroundEstimatorNet(nn.Module):
                     lab = torch.empty((B, N), dtype=torch.float64, device=dev)
             l8 = lab if (lab is not None and lab.dtype == torch.int8) else None
             l64 = lab if (lab is not None and lab.dtype == torch.float64) else None
-            _lib.check(L.gnd_infer(ctx, _lib.ptr(points), _lib.ptr(counts), B, N, float(threshold), _lib.ptr(height),
-                                   _lib.ptr(l8), _lib.ptr(l64), _lib.stream_ptr()), "gnd_infer")
+            for _ in range(2):
+                _lib.check(L.gnd_infer(ctx, _lib.ptr(points), _lib.ptr(counts), B, N, float(threshold), _lib.ptr(height),
+                                       _lib.ptr(l8), _lib.ptr(l64), _lib.stream_ptr()), "gnd_infer")
+                if not self._weights_stale():         # checked behind the launches; a changed parameter re-runs once
+                    break
             self.launches = self.last_launch_count()
         if single:
             return height[0], (lab[0] if lab is not None else None)
@@ -422,7 +444,10 @@ class GroundEstimatorNet(nn.Module):
             return (np.array(conv[:8 * r], dtype=np.float32).reshape(r, 8), np.array(seg[:r], dtype=np.float32))
 
     def pillars(self, batch):
-        """Voxelizer outputs of the last infer() as tensors (views of the workspace)."""
+        """Voxelizer outputs of the last infer() as tensors (views of the workspace): coors, num_points, voxel_count,
+        point_offsets, and the kept points grouped by CELL (cell_offsets [B, cells + 1], cell_points [B, N, 4]).
+        ``point_list`` (per-pillar point indices in slot order) is filled only when the order-exact voxelizer ran
+        (``set_option("vox_path", 1)``, or the stage / drop-in APIs): the fused path keeps sets, not slot order."""
         mv = int(getattr(self.cfg, "max_voxels", self.nx * self.ny * self.nz))
         Bb = self._bound[0]
         N = self._last_n                     # row stride of the per-point buffers = the n_points of that call
@@ -432,4 +457,6 @@ class GroundEstimatorNet(nn.Module):
             voxel_count=self.buffer("voxel_count", torch.int32, (Bb,))[:batch],
             point_offsets=self.buffer("point_offsets", torch.int32, (Bb, mv + 1))[:batch],
             point_list=self.buffer("point_list", torch.int32)[:batch * max(N, 1)].view(batch, max(N, 1)),
+            cell_offsets=self.buffer("cell_offsets", torch.int32, (Bb, self.nx * self.ny * self.nz + 1))[:batch],
+            cell_points=self.buffer("cell_points", torch.float32)[:batch * max(N, 1) * 4].view(batch, max(N, 1), 4),
         )

@@ -124,8 +124,8 @@ class GraphedInfer:
             self._wver = model._weights_version
 
     def __call__(self, points=None):
-        if self.model._bound != self._bound or self.model._params_version() != self._wver:
-            raise RuntimeError("the model's workspace or weights changed after the graph was captured; build a new GraphedInfer")
+        if self.model._bound != self._bound:
+            raise RuntimeError("the model's workspace was re-bound after the graph was captured; build a new GraphedInfer")
         if points is not None:
             if self.counts is not None:
                 if points.dim() == 2:
@@ -138,6 +138,8 @@ class GraphedInfer:
             else:
                 self.points.copy_(points.reshape(self.points.shape), non_blocking=True)
         self.graph.replay()
+        if self.model._params_version() != self._wver:      # behind the replay: off the latency path
+            raise RuntimeError("the model's weights changed after the graph was captured; build a new GraphedInfer")
         return self.height, self.labels
 
 

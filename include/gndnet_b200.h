@@ -211,7 +211,9 @@ GND_API int gnd_segnet_profile(gnd_ctx *ctx, int32_t batch, float *height, float
 GND_API int gnd_segment(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
                         int64_t n_points, const float *height, double threshold, int8_t *labels_i8,
                         double *labels_f64, void *stream);
-/* Stages 1-4 back to back on `stream`. */
+/* Stages 1-4 back to back on `stream`.  The voxelization inside is set-exact (see gnd_set_option "vox_path"): pillar
+ * ids, coors, num_points and every pillar's kept points equal the reference's; the per-pillar point index lists in
+ * slot order are only materialised by gnd_voxelize / gnd_points_to_voxel. */
 GND_API int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
                       int64_t n_points, double threshold, float *height, int8_t *labels_i8,
                       double *labels_f64, void *stream);
@@ -288,7 +290,10 @@ GND_API int gnd_get_buffer(gnd_ctx *ctx, const char *name, void **ptr, size_t *b
 GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
 /* Per-ctx switches (tests, A/B timing; never read from the environment at launch time):
  *   "conv_path"      0 = CTA-pair halo kernel where the shape fits (default), 1 = single-CTA tap kernel (the fallback)
- *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel */
+ *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel
+ *   "vox_path"       gnd_infer only: 0 = set-exact voxelization (default: same coors / num_points / voxel_count / offsets
+ *                    and the same kept points per pillar, but no slot-ordered point_list), 1 = the order-exact kernels
+ *                    gnd_voxelize uses (point_list filled) */
 GND_API int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value);
 /* Asynchronous per-convolution timing for bench.py's roofline: after _begin, each of the next `slots` gnd_segnet /
  * gnd_infer calls records library-owned CUDA events around its 8 convolution launches (nothing is read back, the

@@ -142,3 +142,57 @@ def test_maximum_sizes(cuda):
     with pytest.raises(_lib.GndError) as ei:
         points_to_voxel(pts, [0.5, 0.5, 8], [-79.5, -79, -4, 79, 79, 4], 35, True, 20000)     # 317 x 316 cells
     assert ei.value.code == -4
+
+
+LEAN_CASES = ["hdl64_s0", "uniform_s0", "real_000000", "boundary_kitti", "single_cell", "overflow_64", "overflow_1000",
+              "overflow_5000", "maxpts_5", "small_kitti", "empty", "all_outside", "one_point", "boundary_camera",
+              "small_camera", "camera_1m"]
+
+
+@pytest.mark.parametrize("name", LEAN_CASES)
+def test_fused_set_exact_voxelizer_equals_order_exact(name, cuda):
+    """gnd_infer voxelizes with the set-exact kernels (no per-point ranking).  Against the order-exact kernels on the
+    same scans: identical coors / num_points / voxel_count / offsets, identical SET of kept points in every cell, and --
+    the pillar encoder being order-independent inside a pillar -- bit-identical height maps and labels.  And against the
+    oracle: coors / num_points equal the reference's."""
+    from tests import helpers
+    cfgname, gen, ov = cases.CASES[name]
+    cfg, raw, gold = cases.load_case(name)
+    cfg.batch_size = 1
+    model, sd = helpers.load_model(cfg, cfgname, "mixed", cuda)
+    pts = torch.from_numpy(raw).cuda().unsqueeze(0).contiguous()
+    if raw.shape[0] == 0:
+        pts = torch.zeros((1, 4, cfg.input_features), device="cuda")
+    counts = torch.tensor([raw.shape[0]], dtype=torch.int32, device="cuda")
+    out = {}
+    with torch.no_grad():
+        for path in (1, 0, 0):                      # exact, set-exact, set-exact again (self-resetting state)
+            model.set_option("vox_path", path)
+            h, l = model.infer(pts, threshold=0.08, counts=counts, labels="int8")
+            pil = {k: v.clone() for k, v in model.pillars(1).items()}
+            out.setdefault(path, []).append((h.clone(), l.clone(), pil))
+    (he, le, pe), = out[1]
+    for hl, ll, pl in out[0]:
+        m = int(pe["voxel_count"][0])
+        assert int(pl["voxel_count"][0]) == m == gold["M"]
+        assert torch.equal(pl["coors"][0, :m], pe["coors"][0, :m])
+        assert torch.equal(pl["num_points"][0, :m], pe["num_points"][0, :m])
+        assert torch.equal(pl["point_offsets"][0, :m + 1], pe["point_offsets"][0, :m + 1])
+        assert torch.equal(pl["cell_offsets"], pe["cell_offsets"])
+        kept = int(pe["cell_offsets"][0, -1])
+        assert kept == gold["kept"]
+        # same set of points per cell: sort the rows of every cell (cells are contiguous runs of cell_points)
+        offs = pe["cell_offsets"][0].long()
+        seg = torch.repeat_interleave(torch.arange(offs.numel() - 1, device="cuda"), offs[1:] - offs[:-1])
+
+        def canon(rows):
+            rows = rows[:kept]
+            order = torch.arange(kept, device="cuda")
+            for col in (3, 2, 1, 0):                  # lexicographic by successive stable sorts, then by cell
+                order = order[torch.argsort(rows[order, col], stable=True)]
+            order = order[torch.argsort(seg[order], stable=True)]
+            return rows[order]
+        assert torch.equal(canon(pl["cell_points"][0]), canon(pe["cell_points"][0])), "kept point sets differ"
+        assert torch.equal(hl, he) and torch.equal(ll, le), "set-exact voxelization changed the result"
+    assert synth.digest(pe["coors"][0, :gold["M"]].cpu().numpy()) == gold["coors_digest"]
+    assert synth.digest(pe["num_points"][0, :gold["M"]].cpu().numpy()) == gold["num_points_digest"]
