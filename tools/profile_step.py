@@ -15,12 +15,15 @@ ap.add_argument("--batch", type=int, default=64)
 ap.add_argument("--steps", type=int, default=2)
 ap.add_argument("--precision", default="mixed")
 ap.add_argument("--cfg", default="kitti")
+ap.add_argument("--vox-path", type=int, default=0, help="1: order-exact voxelizer kernels inside infer()")
 args = ap.parse_args()
 cfg = synth.make_cfg(args.cfg)
 sd, _ = synth.checkpoint(args.cfg)
 model = GroundEstimatorNet(cfg, precision=args.precision)
 model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
 model = model.cuda().eval()
+if args.vox_path:
+    model.set_option("vox_path", args.vox_path)
 base = [synth.hdl64_scan(s) if args.cfg == "kitti" else synth.camera_scan(s) for s in range(4)]
 pts = torch.from_numpy(np.stack([base[i % 4] for i in range(args.batch)])).cuda()
 with torch.no_grad():
