@@ -272,6 +272,192 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
     }
 }
 
+// ---- the same, with the per-point Linear on the (legacy-path) tensor cores --------------------------------------
+// ncu on pfn_scatter_kernel: 135 M warp instructions per 64 scans, 31 per kept point, issue-bound (71 % busy); the
+// multiply-adds themselves are a third of that.  Here a warp still owns a cell, but its points go through
+// mma.sync.m16n8k8 (TF32 operands, fp32 accumulate) 16 at a time:
+//   A [16 points x 8]  = [ hi(x', y', z, r) | lo(x', y', z, r) ]        hi = tf32(v), lo = tf32(v - hi)
+//   B1 [8 x 8 ch]      = [ W'hi ; W'hi ],   B2 = [ W'lo ; 0 ]            W' = the regrouped weights A, B, C, D above
+//   A B1 + A B2        = hi W'hi + lo W'hi + hi W'lo                     (3xTF32: ~2^-21 relative, fp32 class)
+// two MMAs per 8 channels and 16 points, i.e. ONE tensor instruction per point for all 64 channels, against 8 FFMA +
+// 1 LDS on the CUDA cores; the running maximum is taken on the accumulator fragments (rows g and g + 8 of a thread),
+// folded across the 8 row groups at the end of the cell by a 3-round reduce-scatter that leaves lane (g, t) with
+// channels 8 g + 2 t, 8 g + 2 t + 1.  The pillar mean keeps its order-independent fixed-point form (identical sums,
+// so an identical E term); each thread sums the one feature it loads.  No shared memory, one pass over the points.
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                uint32_t b0, uint32_t b1, const float (&c)[4]) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c[0]), "f"(c[1]), "f"(c[2]), "f"(c[3]));
+}
+
+template <bool HAS_R>
+__global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_mma_kernel(const PfnArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    constexpr int kf = HAS_R ? 4 : 3;
+    auto W = [&](int k, int ch) { return __ldg(a.w + k * PFN_OUT + ch); };
+    // B fragments: row k = t of the regrouped weights, column g of every 8-channel tile
+    uint32_t bhi[8], blo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int ch = 8 * j + g;
+        float w;
+        if (t == 0) w = W(0, ch) + W(kf, ch) + W(kf + 3, ch);
+        else if (t == 1) w = W(1, ch) + W(kf + 1, ch) + W(kf + 4, ch);
+        else if (t == 2) w = W(2, ch) + W(kf + 2, ch);
+        else w = HAS_R ? W(3, ch) : 0.0f;
+        bhi[j] = to_tf32(w);
+        blo[j] = to_tf32(w - __uint_as_float(bhi[j]));
+    }
+    // the two channels this lane finalises
+    const int ch0 = 8 * g + 2 * t, ch1 = ch0 + 1;
+    const float wx0 = W(0, ch0), wx1 = W(0, ch1), wy0 = W(1, ch0), wy1 = W(1, ch1);
+    const float wmx0 = W(kf, ch0), wmx1 = W(kf, ch1), wmy0 = W(kf + 1, ch0), wmy1 = W(kf + 1, ch1);
+    const float wmz0 = W(kf + 2, ch0), wmz1 = W(kf + 2, ch1);
+    const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
+    const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
+    const float qscale = (t < 2) ? a.q_xy : (t == 2 ? a.q_z : 0.0f);
+    const float qoff = (t == 2) ? a.zmid : 0.0f;
+    const int cells = a.nx * a.ny;
+    const int gsize = 1 << a.gshift;
+    const int groups = (cells + gsize - 1) >> a.gshift;
+    const int total = a.B * groups;
+    for (;;) {
+        int grp = 0;
+        if (lane == 0) grp = atomicAdd(a.ctr, 1);
+        grp = __shfl_sync(0xffffffffu, grp, 0);
+        if (grp >= total) break;
+        const int b = grp / groups, c0 = (grp - b * groups) << a.gshift;
+        const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
+        const float *pts = reinterpret_cast<const float *>(a.sorted + (int64_t)b * a.N);
+        const int cl = min(c0 + lane, cells);
+        const int my_o = __ldg(offc + cl);
+        const int my_n = __ldg(offc + min(cl + 1, cells)) - my_o;
+        const int ncell = min(gsize, cells - c0);
+        if (lane < ncell && my_n == 0) {           // empty cells: the owning lane writes the 64 zeros
+            const int64_t o = ((int64_t)b * cells + c0 + lane) * PFN_OUT;
+            const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+            if (a.out32) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k) reinterpret_cast<uint4 *>(a.out32 + o)[k] = z4;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_hi + o)[k] = z4;
+                if (a.out_lo) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_lo + o)[k] = z4;
+                }
+            }
+        }
+        const int my_cy = cl / a.nx, my_cx = cl - my_cy * a.nx;
+        unsigned occ = __ballot_sync(0xffffffffu, lane < ncell && my_n > 0);
+        while (occ) {
+            const int jc = __ffs(occ) - 1;
+            occ &= occ - 1;
+            const int n = __shfl_sync(0xffffffffu, my_n, jc);
+            const int o = __shfl_sync(0xffffffffu, my_o, jc);
+            const int cx = __shfl_sync(0xffffffffu, my_cx, jc), cy = __shfl_sync(0xffffffffu, my_cy, jc);
+            // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
+            const float pcx = __fadd_rn(__fmul_rn((float)cx, a.vx), a.xoff);
+            const float pcy = __fadd_rn(__fmul_rn((float)cy, a.vy), a.yoff);
+            const float sub = (t == 0) ? pcx : (t == 1 ? pcy : 0.0f);
+            float m[8][2];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { m[j][0] = -INFINITY; m[j][1] = -INFINITY; }
+            int qsum = 0;
+            const float *cell_pts = pts + (int64_t)o * 4 + t;
+            for (int r0 = 0; r0 < n; r0 += 16) {
+                const int row0 = r0 + g, row1 = row0 + 8;
+                // rows past the end repeat the last point: the maximum does not change, the mean skips them
+                const float v0 = __ldg(cell_pts + 4 * min(row0, n - 1)) - sub;
+                const float v1 = __ldg(cell_pts + 4 * min(row1, n - 1)) - sub;
+                if (row0 < n) qsum += __float2int_rn((v0 - qoff) * qscale);
+                if (row1 < n) qsum += __float2int_rn((v1 - qoff) * qscale);
+                const uint32_t a0 = to_tf32(v0), a1 = to_tf32(v1);
+                const uint32_t a2 = to_tf32(v0 - __uint_as_float(a0)), a3 = to_tf32(v1 - __uint_as_float(a1));
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float zero[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                    float c1[4], c2[4];
+                    mma_tf32_16x8x8(c1, a0, a1, a2, a3, blo[j], 0u, zero);          // hi W'lo (small terms first)
+                    mma_tf32_16x8x8(c2, a0, a1, a2, a3, bhi[j], bhi[j], c1);        // + hi W'hi + lo W'hi
+                    m[j][0] = fmaxf(m[j][0], fmaxf(c2[0], c2[2]));
+                    m[j][1] = fmaxf(m[j][1], fmaxf(c2[1], c2[3]));
+                }
+            }
+            // feature sums over the 8 row groups (lanes with the same t)
+            qsum += __shfl_xor_sync(0xffffffffu, qsum, 4);
+            qsum += __shfl_xor_sync(0xffffffffu, qsum, 8);
+            qsum += __shfl_xor_sync(0xffffffffu, qsum, 16);
+            const int qx = __shfl_sync(0xffffffffu, qsum, 0), qy = __shfl_sync(0xffffffffu, qsum, 1);
+            const int qz = __shfl_sync(0xffffffffu, qsum, 2);
+            // maxima: reduce-scatter over the row groups; lane (g, t) ends with tile g, i.e. channels 8 g + 2 t, + 1
+            float r4[4][2], r2[2][2], r1[2];
+            {
+                const bool low = (g & 4) == 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        const float send = low ? m[4 + i][k] : m[i][k];
+                        const float recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                        r4[i][k] = fmaxf(low ? m[i][k] : m[4 + i][k], recv);
+                    }
+            }
+            {
+                const bool low = (g & 2) == 0;
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        const float send = low ? r4[2 + i][k] : r4[i][k];
+                        const float recv = __shfl_xor_sync(0xffffffffu, send, 8);
+                        r2[i][k] = fmaxf(low ? r4[i][k] : r4[2 + i][k], recv);
+                    }
+            }
+            {
+                const bool low = (g & 1) == 0;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const float send = low ? r2[1][k] : r2[0][k];
+                    const float recv = __shfl_xor_sync(0xffffffffu, send, 4);
+                    r1[k] = fmaxf(low ? r2[0][k] : r2[1][k], recv);
+                }
+            }
+            const float rn = __frcp_rn((float)n);
+            const float mxr = (float)qx * (rn * a.iq_xy), myr = (float)qy * (rn * a.iq_xy);   // mean(x'), mean(y')
+            const float mz = a.zmid + (float)qz * (rn * a.iq_z);
+            const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(-wmx0, mxr, fmaf(-wmy0, myr, fmaf(-wmz0, mz, b0)))));
+            const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(-wmx1, mxr, fmaf(-wmy1, myr, fmaf(-wmz1, mz, b1)))));
+            // padded slots give relu(b') (:137-140 then :54-58)
+            const float o0 = fmaxf(r1[0] + E0, n < a.P ? rb0 : 0.0f);
+            const float o1 = fmaxf(r1[1] + E1, n < a.P ? rb1 : 0.0f);
+            const int64_t oidx = ((int64_t)b * cells + c0 + jc) * PFN_OUT + ch0;
+            if (a.out32) {
+                *reinterpret_cast<float2 *>(a.out32 + oidx) = make_float2(o0, o1);
+            } else {
+                const __half2 hh = __floats2half2_rn(o0, o1);
+                *reinterpret_cast<__half2 *>(a.out_hi + oidx) = hh;
+                if (a.out_lo) {
+                    const float2 back = __half22float2(hh);
+                    *reinterpret_cast<__half2 *>(a.out_lo + oidx) = __floats2half2_rn(o0 - back.x, o1 - back.y);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(a.ctr + 1, 1) == (int)gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; __threadfence(); }
+    }
+}
+
 // Drop-in tensors (model.py:36-42): voxels [M][P][F], coors [M][4] float (b,z,y,x), num_points [M] float.
 // The canvas must have been zero-filled (pointpillars.py:174).
 __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_dense_kernel(const PfnArgs a) {
@@ -362,6 +548,13 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically
     const bool has_r = ctx->cfg.input_features > 3;
+    if (!ctx->cfg.with_distance && ctx->opt_pfn_path == 0) {      // tensor-core variant (no |p| feature: four regrouped inputs)
+        if (blocks > 148 * 3) blocks = 148 * 3;
+        if (has_r) pfn_scatter_mma_kernel<true><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+        else pfn_scatter_mma_kernel<false><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
+        GND_LAUNCH_CHECK("pfn_scatter_mma_kernel");
+        return GND_OK;
+    }
     if (ctx->cfg.with_distance) {
         if (has_r) pfn_scatter_kernel<true, true><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
         else pfn_scatter_kernel<true, false><<<blocks, PFN_WARPS * 32, 0, st>>>(a);

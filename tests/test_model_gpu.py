@@ -137,6 +137,41 @@ def test_fused_infer_end_to_end(cfgname, scans, overrides, precision, cuda):
     assert same / total >= 0.999
 
 
+def _canvas(model, B, precision):
+    if precision == "fp32":
+        return model.buffer("canvas", torch.float32, (B, model.ny, model.nx, 64)).permute(0, 3, 1, 2).cpu()
+    return (model.buffer("canvas.hi", torch.float16, (B, model.ny, model.nx, 64)).float()
+            + model.buffer("canvas.lo", torch.float16, (B, model.ny, model.nx, 64)).float()).permute(0, 3, 1, 2).cpu()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "split"])
+@pytest.mark.parametrize("cfgname,scans,overrides", [("kitti", ["hdl64_s0", "uniform_s0", "real_000000"], {}),
+                                                     ("kitti", ["small_kitti"], dict(use_norm=True)),
+                                                     ("camera", ["small_camera"], {}),
+                                                     ("camera", ["camera_1m"], {}),
+                                                     ("kitti", ["overflow_1000"], dict(max_voxels=1000))])
+def test_fused_pillar_encoders_match_oracle_canvas(cfgname, scans, overrides, precision, cuda):
+    """The two fused pillar encoders (mma.sync TF32x3 and CUDA-core) against the oracle's BEV canvas
+    (pillar_encoder.py:104-147 + PointPillarsScatter :170-199), and against each other."""
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, scans, overrides, precision, cuda)
+    nmax = max(len(r) for r in raws)
+    batch = np.full((len(raws), nmax, cfg.input_features), 1e9, dtype=np.float32)
+    for b, r in enumerate(raws):
+        batch[b, :len(r)] = r
+    counts = torch.tensor([len(r) for r in raws], dtype=torch.int32).cuda()
+    scale = max(1.0, st["canvas"].abs().max().item())
+    got = {}
+    for path in (0, 1):
+        model.set_option("pfn_path", path)
+        with torch.no_grad():
+            model.infer(torch.from_numpy(batch).cuda(), threshold=0.08, counts=counts, labels=None)
+        got[path] = _canvas(model, len(raws), precision)
+        dc = (got[path] - st["canvas"]).abs().max().item()
+        print("pfn_path %d: canvas max|d| = %.3g (scale %.3g)" % (path, dc, scale))
+        assert dc <= 2e-5 * scale, "pfn_path %d: canvas differs by %g" % (path, dc)
+    assert (got[0] - got[1]).abs().max().item() <= 4e-6 * scale
+
+
 def test_state_dict_keys_match_reference_layout(cuda):
     from gndnet_b200.model import GroundEstimatorNet
     for cfgname, ov in (("kitti", {}), ("camera", {}), ("kitti", dict(use_norm=True))):
