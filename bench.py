@@ -574,7 +574,7 @@ def main():
             model.conv_timing_begin(n_t)
             for i in range(n_t):
                 step_resident(i)
-            conv_ms_all, seg_ms_all = model.conv_timing_end()
+            conv_ms_all, seg_ms_all, stage_ms_all = model.conv_timing_end(stages=True)
         conv_layers = conv_ms_all.mean(axis=0)
         conv_ms = float(conv_layers.sum())
         alg_gflop = (GFLOP_PER_SCAN - 0.0115) * B
@@ -654,8 +654,15 @@ def main():
             torch.cuda.synchronize()
             soak(step_resident, 0.3)
             st = model.stage_times(resident[1], height, labels, reps=5)
+        extra["stage_ms_stage_calls"] = st
+        extra["stage_ms_stage_calls_note"] = ("the four stage entry points of the C ABI (gnd_voxelize = the ORDER-exact voxelizer that "
+                                              "also fills point_list), 5 steps with a host sync between steps, after a 0.3 s soak")
+        # the stages as infer() ran them inside the long back-to-back run above (set-exact voxelizer on this workload)
+        sm = stage_ms_all[stage_ms_all[:, 0] >= 0].mean(axis=0)
+        st = dict(st, voxelize=float(sm[0]), pfn_scatter=float(sm[1]), segnet=float(sm[2]), segment=float(sm[3]))
         extra["stage_ms"] = st
-        extra["stage_ms_note"] = "5 steps with a host sync between steps, right after a 0.3 s soak"
+        extra["stage_ms_note"] = ("voxelize / pfn_scatter / segnet / segment: CUDA events between the stages of gnd_infer, averaged over "
+                                  "%d consecutive steps of a long run (sustained clocks)" % len(stage_ms_all))
         # the HBM-bound stages: algorithmic bytes (SURVEY.md 8d / DESIGN.md 5) over the measured stage time
         pil = model.pillars(B)
         M = pil["voxel_count"].long()

@@ -88,7 +88,7 @@ _SIGS = {
     "gnd_last_launch_count": (ctypes.c_int, [c_vp]),
     "gnd_set_option": (ctypes.c_int, [c_vp, ctypes.c_char_p, c_i32]),
     "gnd_conv_timing_begin": (ctypes.c_int, [c_vp, c_i32]),
-    "gnd_conv_timing_end": (ctypes.c_int, [c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_f), ctypes.POINTER(c_i32)]),
+    "gnd_conv_timing_end": (ctypes.c_int, [c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_f), ctypes.POINTER(c_f), ctypes.POINTER(c_i32)]),
 }
 
 _lib = None

@@ -175,6 +175,7 @@ extern "C" int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value) {
 static void timing_free(gnd_ctx *ctx) {
     for (cudaEvent_t e : ctx->tim_events) cudaEventDestroy(e);
     ctx->tim_events.clear();
+    ctx->tim_staged.clear();
     ctx->tim_slots = ctx->tim_next = 0;
 }
 
@@ -182,23 +183,32 @@ extern "C" int gnd_conv_timing_begin(gnd_ctx *ctx, int32_t slots) {
     if (!ctx || slots < 1 || slots > 4096) return fail(GND_ERR_INVALID, "slots must be 1..4096");
     GND_CUDA_CHECK(cudaSetDevice(ctx->device));
     timing_free(ctx);
-    ctx->tim_events.resize((size_t)slots * 18);
+    ctx->tim_events.resize((size_t)slots * TIM_STRIDE);
     for (cudaEvent_t &e : ctx->tim_events) GND_CUDA_CHECK(cudaEventCreate(&e));
+    ctx->tim_staged.assign((size_t)slots, 0);
     ctx->tim_slots = slots;
     return GND_OK;
 }
 
-extern "C" int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, int32_t *h_recorded) {
+extern "C" int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, float *h_stage_ms, int32_t *h_recorded) {
     if (!ctx || !h_conv_ms || !h_segnet_ms || !h_recorded) return fail(GND_ERR_INVALID, "null argument");
     GND_CUDA_CHECK(cudaSetDevice(ctx->device));
     const int n = ctx->tim_next;
     *h_recorded = n;
     int rc = GND_OK;
     for (int s = 0; s < n && rc == GND_OK; ++s) {
-        cudaEvent_t *ev = &ctx->tim_events[(size_t)s * 18];
-        cudaError_t e = cudaEventSynchronize(ev[17]);
+        cudaEvent_t *ev = &ctx->tim_events[(size_t)s * TIM_STRIDE];
+        const bool staged = ctx->tim_staged.size() > (size_t)s && ctx->tim_staged[s];
+        cudaError_t e = cudaEventSynchronize(ev[staged ? 21 : 17]);
         for (int l = 0; l < 8 && e == cudaSuccess; ++l) e = cudaEventElapsedTime(&h_conv_ms[s * 8 + l], ev[2 * l], ev[2 * l + 1]);
         if (e == cudaSuccess) e = cudaEventElapsedTime(&h_segnet_ms[s], ev[16], ev[17]);
+        if (h_stage_ms) {        // gnd_infer calls: voxelize, pillar-encode + scatter, segnet, labels; -1 for other calls
+            static const int from[4] = {18, 19, 16, 20}, to[4] = {19, 16, 17, 21};
+            for (int k = 0; k < 4; ++k) {
+                h_stage_ms[s * 4 + k] = -1.0f;
+                if (staged && e == cudaSuccess) e = cudaEventElapsedTime(&h_stage_ms[s * 4 + k], ev[from[k]], ev[to[k]]);
+            }
+        }
         if (e != cudaSuccess) rc = fail(GND_ERR_CUDA, "conv timing read-back: %s", cudaGetErrorString(e));
     }
     timing_free(ctx);
@@ -305,6 +315,11 @@ extern "C" int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *count
     if (rc != GND_OK) return rc;
     if (!height) return fail(GND_ERR_INVALID, "height is null");
     cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t *sev = nullptr;          // armed by gnd_conv_timing_begin: this call's slot also gets the stage events
+    if (ctx->tim_next < ctx->tim_slots) {
+        sev = &ctx->tim_events[(size_t)ctx->tim_next * TIM_STRIDE];
+        cudaEventRecord(sev[18], st);
+    }
     // the fused path needs per cell the SET of kept points, not the slot-ordered index lists: set-exact kernels
     // (voxelize.cu); gnd_voxelize / gnd_points_to_voxel keep producing the lists with the order-exact ones
     // ... unless the cloud is dense (the camera frames: ~400 points in every cell, all over-full): there the candidate
@@ -317,10 +332,17 @@ extern "C" int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *count
     else
         rc = vox_run(&ctx->vparams, ctx->vplan, ctx->vws, points, counts, batch, n_points, ctx->coors, ctx->num_points,
                      ctx->voxel_count, ctx->offsets, ctx->list, nullptr, nullptr, st);
+    if (sev) cudaEventRecord(sev[19], st);
     if (rc == GND_OK) rc = pfn_scatter_run(ctx, points, batch, n_points, st);
-    if (rc == GND_OK) rc = segnet_run(ctx, batch, height, st);
+    const int slot = ctx->tim_next;
+    if (rc == GND_OK) rc = segnet_run(ctx, batch, height, st);       // takes the slot (events 0..17)
+    if (sev) cudaEventRecord(sev[20], st);
     if (rc == GND_OK && (labels_i8 || labels_f64) && n_points > 0)
         rc = segment_with_ctx(ctx, points, counts, batch, n_points, height, threshold, labels_i8, labels_f64, st);
+    if (sev) {
+        cudaEventRecord(sev[21], st);
+        if (rc == GND_OK && ctx->tim_next == slot + 1) ctx->tim_staged[slot] = 1;
+    }
     ctx->last_launches = g_launches;
     return rc;
 }

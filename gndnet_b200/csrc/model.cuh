@@ -11,6 +11,7 @@ namespace gnd {
 
 constexpr int PFN_OUT = 64;        // cfg.vfe_filters = [64] in every shipped config
 constexpr int PFN_MAX_FEAT = 10;
+constexpr int TIM_STRIDE = 22;     // events per slot of the timing ring (gnd_conv_timing_begin)
 constexpr int BN_BLOCKS = 592;     // partial-sum blocks of the batch-statistics reduction   // F(<=4) + 3 + 2 + with_distance
 
 // A BEV activation tensor, NHWC ([B][H][W][C]).  fp32 mode: one float plane.  tcgen05 modes: an fp16
@@ -83,7 +84,8 @@ struct gnd_ctx {
 
     // gnd_conv_timing_begin / _end: library-owned ring of CUDA events around the 8 convolution launches of every
     // gnd_segnet / gnd_infer while armed (asynchronous: nothing is read back until _end)
-    std::vector<cudaEvent_t> tim_events;     // [slots][18]
+    std::vector<cudaEvent_t> tim_events;     // [slots][TIM_STRIDE]: 0..15 conv launches, 16/17 segnet, 18..21 gnd_infer stages
+    std::vector<char> tim_staged;            // slot was filled by gnd_infer (stage events valid)
     int tim_slots = 0, tim_next = 0;
 };
 

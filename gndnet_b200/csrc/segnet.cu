@@ -427,7 +427,7 @@ int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEven
     int rc;
     bool ring = false;
     if (!ev && ctx->tim_next < ctx->tim_slots) {          // armed by gnd_conv_timing_begin: next slot of the event ring
-        ev = &ctx->tim_events[(size_t)ctx->tim_next++ * 18];
+        ev = &ctx->tim_events[(size_t)ctx->tim_next++ * TIM_STRIDE];
         ring = true;
         cudaEventRecord(ev[16], st);
     }

@@ -432,16 +432,21 @@ class GroundEstimatorNet(nn.Module):
             _lib.check(_lib.lib().gnd_conv_timing_begin(self._ctx, int(slots)), "gnd_conv_timing_begin")
             self._tim_slots = int(slots)
 
-    def conv_timing_end(self):
-        """-> (conv_ms [recorded, 8], segnet_ms [recorded]) float32 arrays; waits for the recorded events."""
+    def conv_timing_end(self, stages=False):
+        """-> (conv_ms [recorded, 8], segnet_ms [recorded]) float32 arrays; waits for the recorded events.  With
+        ``stages`` also stage_ms [recorded, 4] (voxelize, pillar-encode + scatter, segnet, labels as infer() ran them)."""
         with self._lock:
             n = self._tim_slots
             conv = (ctypes.c_float * (8 * n))()
             seg = (ctypes.c_float * n)()
+            stg = (ctypes.c_float * (4 * n))()
             rec = ctypes.c_int32()
-            _lib.check(_lib.lib().gnd_conv_timing_end(self._ctx, conv, seg, ctypes.byref(rec)), "gnd_conv_timing_end")
+            _lib.check(_lib.lib().gnd_conv_timing_end(self._ctx, conv, seg, stg, ctypes.byref(rec)), "gnd_conv_timing_end")
             r = rec.value
-            return (np.array(conv[:8 * r], dtype=np.float32).reshape(r, 8), np.array(seg[:r], dtype=np.float32))
+            out = (np.array(conv[:8 * r], dtype=np.float32).reshape(r, 8), np.array(seg[:r], dtype=np.float32))
+            if stages:
+                out = out + (np.array(stg[:4 * r], dtype=np.float32).reshape(r, 4),)
+            return out
 
     def pillars(self, batch):
         """Voxelizer outputs of the last infer() as tensors (views of the workspace): coors, num_points, voxel_count,

@@ -301,9 +301,10 @@ GND_API int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value);
 /* Asynchronous per-convolution timing for bench.py's roofline: after _begin, each of the next `slots` gnd_segnet /
  * gnd_infer calls records library-owned CUDA events around its 8 convolution launches (nothing is read back, the
  * stream is not synchronised); _end waits for them, writes h_conv_ms[recorded][8] and h_segnet_ms[recorded] (device
- * milliseconds) and frees the events. */
+ * milliseconds) and frees the events.  h_stage_ms (may be NULL) [recorded][4]: for slots filled by gnd_infer, the device
+ * time of its four stages as that call ran them -- voxelize, pillar-encode + scatter, segnet, labels -- else -1. */
 GND_API int gnd_conv_timing_begin(gnd_ctx *ctx, int32_t slots);
-GND_API int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, int32_t *h_recorded);
+GND_API int gnd_conv_timing_end(gnd_ctx *ctx, float *h_conv_ms, float *h_segnet_ms, float *h_stage_ms, int32_t *h_recorded);
 
 #ifdef __cplusplus
 }

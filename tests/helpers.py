@@ -100,7 +100,9 @@ def flip_mask(model, st, tie_rel=2e-3, tie_abs=1e-4):
 # near-tie flip; ON TOP of that the unmasked map must meet the bar on all but MAX_FRAC_OVER of its pixels, the mask may
 # cover at most MAX_FRAC_MASKED of it, and the worst pixel anywhere is capped (a flip moves one near-tied activation by
 # one pixel: the output changes around it, it does not blow up).
-# Measured on the B200 (profiles/r2_parity_report.md): 0-4 flips per case, each a <= 2e-3 relative near-tie in the
+# The two fractions are quoted on the kittiSem 100x100 map and scale with map area (a flip touches a fixed number of
+# PIXELS, so the 50x50 camera map gets 4x the fraction: _area_scale).
+# Measured on the B200 (profiles/r2_parity_report.jsonl): 0-4 flips per case, each a <= 2e-3 relative near-tie in the
 # oracle; one level-1 flip touches <= 8x8 output pixels, one level-2 flip <= 18x18 (0.64 % / 3.2 % of a 100x100 map,
 # 2.6 % / 13 % of the 50x50 camera map); worst unmasked over-bar fraction 2.2 %, worst pixel 0.33 m.  The strict
 # fp32 CUDA-core mode flips too (another summation order is enough), so this is a property of MaxPool / MaxUnpool,
@@ -109,6 +111,11 @@ TOL = {"fp32": 1e-3, "split": 1e-3, "mixed": 5e-3}
 MAX_FRAC_OVER = {"fp32": 0.03, "split": 0.03, "mixed": 0.03}
 MAX_FRAC_MASKED = {"fp32": 0.08, "split": 0.08, "mixed": 0.08}
 MAX_OVERALL = 0.5          # metres
+
+
+def _area_scale(st):
+    _, _, H, W = st["out"].shape
+    return max(1.0, 100.0 * 100.0 / float(H * W))
 
 
 def max_flips(B):
@@ -143,8 +150,9 @@ def assert_heights(rep, precision, st, what=""):
     m1, m2 = max_flips(st["out"].shape[0])
     assert rep["flips"][0] <= m1 and rep["flips"][1] <= m2, "too many argmax flips: " + line
     assert rep["stable_max"] <= TOL[precision], line
-    assert rep["frac_over"] <= MAX_FRAC_OVER[precision], "too many pixels over the bar: " + line
-    assert rep["frac_masked"] <= MAX_FRAC_MASKED[precision], "flip mask too large: " + line
+    k = _area_scale(st)
+    assert rep["frac_over"] <= MAX_FRAC_OVER[precision] * k, "too many pixels over the bar: " + line
+    assert rep["frac_masked"] <= MAX_FRAC_MASKED[precision] * k, "flip mask too large: " + line
     assert rep["overall"] <= MAX_OVERALL, line
 
 
