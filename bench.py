@@ -428,6 +428,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="only value / e2e (profiling runs)")
     ap.add_argument("--soak", type=float, default=0.6, help="seconds of un-timed soak before each timed region")
+    ap.add_argument("--split", type=int, default=0, help="e2e: sub-batches per submitted batch (0: 4 on one GPU, 2 with several ranks)")
     ap.add_argument("--equal-shards", action="store_true", help="e2e: equal shards instead of link-rate-proportional ones")
     ap.add_argument("--ref-scans-per-step", type=int, default=8, help="--impl reference: scans timed per step (bounded sample of the batch)")
     args = ap.parse_args()
@@ -493,7 +494,7 @@ def main():
         rates = [float(x.item()) for x in allr]
     shards = [B] * world if (world == 1 or args.equal_shards) else rate_shards(rates, world * B, max(8, B // 2), Bmax)
     my_b = shards[rank]
-    pipe = ScanStream(model, Bmax, N_POINTS, depth=2, labels="int8", threshold=0.08, split=(2 if world > 1 else 1))
+    pipe = ScanStream(model, Bmax, N_POINTS, depth=2, labels="int8", threshold=0.08, split=(args.split if args.split > 0 else (2 if world > 1 else 4)))
 
     def step_resident(i):
         model.infer(resident[i & 1], threshold=0.08, out=(height, labels))

@@ -157,7 +157,7 @@ extern "C" int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value) {
         if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "conv_path must be 0 (CTA-pair halo kernel) or 1 (single-CTA tap kernel)");
         ctx->opt_conv_path = value;
     } else if (!strcmp(name, "pfn_path")) {
-        if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "pfn_path must be 0 (tensor-core pillar encoder) or 1 (CUDA-core one)");
+        if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "pfn_path must be 0 (automatic), 1 (CUDA-core pillar encoder) or 2 (mma.sync one)");
         ctx->opt_pfn_path = value;
     } else if (!strcmp(name, "vox_path")) {
         if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "vox_path must be 0 (automatic), 1 (order-exact kernels) or 2 (set-exact kernels)");

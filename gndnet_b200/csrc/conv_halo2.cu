@@ -199,7 +199,9 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
     const long long t_entry = clock64();
 #endif
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // pointer arithmetic on the shared array (not an integer round trip): the compiler keeps the shared address space,
+    // so s_bias / s_regw reads are LDS and not generic loads
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *ring_a = smem;
     uint8_t *ring_b = smem + (size_t)H2_SA * p.a_stage;
     uint64_t *bars = reinterpret_cast<uint64_t *>(ring_b + (size_t)p.SB * p.b_stage);
@@ -236,7 +238,8 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
     if (threadIdx.x >= 128) {
         for (int i = threadIdx.x - 128; i < p.Cout && i < 256; i += 128) s_bias[i] = p.bias[i];
         if (p.regpart)
-            for (int i = threadIdx.x - 128; i < 576; i += 128) s_regw[(i & 63) * 12 + (i >> 6)] = p.reg_w[i];   // [tap][c] -> [c][tap]
+            for (int i = threadIdx.x - 128; i < 640; i += 128)       // [tap][c] -> [c][tap]; slot 9 of a row = the conv bias of c
+                s_regw[(i & 63) * 12 + (i >> 6)] = (i < 576) ? p.reg_w[i] : p.bias[i - 576];
     }
     tc_fence_before();
     __syncthreads();
@@ -356,10 +359,11 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
                             const int c = 32 * j + i;
-                            const float xv = fmaxf(__uint_as_float(v[i]) + s_bias[c], 0.0f);
                             const float4 w0 = *reinterpret_cast<const float4 *>(s_regw + c * 12);
                             const float4 w1 = *reinterpret_cast<const float4 *>(s_regw + c * 12 + 4);
-                            const float w8 = s_regw[c * 12 + 8];
+                            const float4 w2 = *reinterpret_cast<const float4 *>(s_regw + c * 12 + 8);     // (tap 8, bias, -, -)
+                            const float xv = fmaxf(__uint_as_float(v[i]) + w2.y, 0.0f);
+                            const float w8 = w2.x;
                             part[0] = fmaf(xv, w0.x, part[0]); part[1] = fmaf(xv, w0.y, part[1]);
                             part[2] = fmaf(xv, w0.z, part[2]); part[3] = fmaf(xv, w0.w, part[3]);
                             part[4] = fmaf(xv, w1.x, part[4]); part[5] = fmaf(xv, w1.y, part[5]);
@@ -378,11 +382,12 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
                         tc_ld_32x32(taddr + 32 * j, v);
                         tc_ld_wait();
                         uint32_t hi[16], lo[16];
-                        const float *bj = s_bias + n0 + 32 * j;
+                        const float4 *bj = reinterpret_cast<const float4 *>(s_bias + n0 + 32 * j);       // 16-byte aligned
 #pragma unroll
                         for (int i = 0; i < 16; ++i) {
-                            const float x0 = fmaxf(__uint_as_float(v[2 * i]) + bj[2 * i], 0.0f);
-                            const float x1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bj[2 * i + 1], 0.0f);
+                            const float4 b4 = bj[i >> 1];
+                            const float x0 = fmaxf(__uint_as_float(v[2 * i]) + ((i & 1) ? b4.z : b4.x), 0.0f);
+                            const float x1 = fmaxf(__uint_as_float(v[2 * i + 1]) + ((i & 1) ? b4.w : b4.y), 0.0f);
                             const __half2 hh = __floats2half2_rn(x0, x1);
                             hi[i] = *reinterpret_cast<const uint32_t *>(&hh);
                             const float2 back = __half22float2(hh);

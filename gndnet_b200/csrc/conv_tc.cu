@@ -65,7 +65,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_cons
                   const __grid_constant__ CUtensorMap tm_b_hi, const __grid_constant__ CUtensorMap tm_b_lo,
                   const ConvParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // pointer arithmetic on the shared array (not an integer round trip): the compiler keeps the shared address space,
+    // so s_bias / s_regw reads are LDS and not generic loads
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)p.stages * p.stage_bytes);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * TC_MAX_STAGES + 4);
     float *s_regw = reinterpret_cast<float *>(tmem_slot + 4);          // 9*64 floats (fused regressor only)

@@ -275,15 +275,20 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
 // ---- the same, with the per-point Linear on the (legacy-path) tensor cores --------------------------------------
 // ncu on pfn_scatter_kernel: 135 M warp instructions per 64 scans, 31 per kept point, issue-bound (71 % busy); the
 // multiply-adds themselves are a third of that.  Here a warp still owns a cell, but its points go through
-// mma.sync.m16n8k8 (TF32 operands, fp32 accumulate) 16 at a time:
-//   A [16 points x 8]  = [ hi(x', y', z, r) | lo(x', y', z, r) ]        hi = tf32(v), lo = tf32(v - hi)
-//   B1 [8 x 8 ch]      = [ W'hi ; W'hi ],   B2 = [ W'lo ; 0 ]            W' = the regrouped weights A, B, C, D above
-//   A B1 + A B2        = hi W'hi + lo W'hi + hi W'lo                     (3xTF32: ~2^-21 relative, fp32 class)
-// two MMAs per 8 channels and 16 points, i.e. ONE tensor instruction per point for all 64 channels, against 8 FFMA +
-// 1 LDS on the CUDA cores; the running maximum is taken on the accumulator fragments (rows g and g + 8 of a thread),
-// folded across the 8 row groups at the end of the cell by a 3-round reduce-scatter that leaves lane (g, t) with
-// channels 8 g + 2 t, 8 g + 2 t + 1.  The pillar mean keeps its order-independent fixed-point form (identical sums,
-// so an identical E term); each thread sums the one feature it loads.  No shared memory, one pass over the points.
+// mma.sync.m16n8k8 (TF32 operands, fp32 accumulate) EIGHT at a time, with the CHANNELS on the M side and the points
+// on the N side:
+//   A1 [16 ch x 8] = [ W'hi | W'hi ],  A2 = [ W'lo | 0 ]      W' = the regrouped weights A, B, C, D above (constant
+//                                                              fragments, built once per warp)
+//   B  [8 x 8 pts] = [ hi(x', y', z, r) ; lo(x', y', z, r) ]   hi = tf32(v), lo = tf32(v - hi)
+//   A1 B + A2 B    = W'hi hi + W'hi lo + W'lo hi               (3xTF32: ~2^-21 relative, fp32 class)
+// Lane (g, t) of the warp loads feature t of point g -- the 8 points of a step are ONE coalesced 128-byte row of the
+// cell-ordered buffer and ARE the B fragment, no shared memory, no shuffles -- and gets back channels x points
+// (2t, 2t+1): the maximum over a step's points is one FMNMX3 per accumulator pair, the running maximum of the cell
+// stays in 8 registers, and only the end of the cell pays a 2-round reduce-scatter over t (6 shuffles) that leaves lane
+// (g, t) with one adjacent channel pair.  (The first version of this kernel had the points on the M side: 16 per step,
+// but the maximum then runs over the row groups g, a 3-round 14-shuffle exchange per cell, and the kernel executed
+// MORE instructions than the CUDA-core one: 149.5 M per 64 scans, 263 us against 186 us.)
+// The pillar mean keeps its order-independent fixed-point form (identical sums, so an identical E term).
 __device__ __forceinline__ uint32_t to_tf32(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -296,34 +301,56 @@ __device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], uint32_t a0, uint
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c[0]), "f"(c[1]), "f"(c[2]), "f"(c[3]));
 }
 
+__device__ __forceinline__ void mma_tf32_16x8x4(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k4.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%7,%7,%7};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "f"(0.0f));
+}
+__device__ __forceinline__ void mma_tf32_16x8x8_acc(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1) {
+    // A = [a0 a1 | a0 a1]: the same 16 x 4 block for both halves of K
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%4,%5}, {%6,%7}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+}
+
+constexpr int PFN_RQ = 128;          // reciprocal table: 1 / n for n < PFN_RQ (max_points_voxel is 100 in every shipped config)
+
 template <bool HAS_R>
-__global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_mma_kernel(const PfnArgs a) {
+__global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_mma_kernel(const PfnArgs a) {
+    __shared__ float4 s_ew[32][3];                 // per lane (g, t): the 12 weights of its channel pair's E term
+    __shared__ float2 s_rq[PFN_RQ];                // (1/n) * iq_xy, (1/n) * iq_z
     const int lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
     constexpr int kf = HAS_R ? 4 : 3;
     auto W = [&](int k, int ch) { return __ldg(a.w + k * PFN_OUT + ch); };
-    // B fragments: row k = t of the regrouped weights, column g of every 8-channel tile
-    uint32_t bhi[8], blo[8];
+    // A fragments.  Tile mt: row g <-> channel 2 (8 mt + g), row g + 8 <-> the channel after it (so that a lane ends up
+    // with an adjacent pair); column t (and t + 4) <-> regrouped weight of input t
+    uint32_t ahi[4][2], alo[4][2];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int ch = 8 * j + g;
-        float w;
-        if (t == 0) w = W(0, ch) + W(kf, ch) + W(kf + 3, ch);
-        else if (t == 1) w = W(1, ch) + W(kf + 1, ch) + W(kf + 4, ch);
-        else if (t == 2) w = W(2, ch) + W(kf + 2, ch);
-        else w = HAS_R ? W(3, ch) : 0.0f;
-        bhi[j] = to_tf32(w);
-        blo[j] = to_tf32(w - __uint_as_float(bhi[j]));
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int ch = 2 * (8 * mt + g) + h;
+            float w;
+            if (t == 0) w = W(0, ch) + W(kf, ch) + W(kf + 3, ch);
+            else if (t == 1) w = W(1, ch) + W(kf + 1, ch) + W(kf + 4, ch);
+            else if (t == 2) w = W(2, ch) + W(kf + 2, ch);
+            else w = HAS_R ? W(3, ch) : 0.0f;
+            ahi[mt][h] = to_tf32(w);
+            alo[mt][h] = to_tf32(w - __uint_as_float(ahi[mt][h]));
+        }
+    // the adjacent channel pair this lane finalises: tile 2 (t & 1) + (t >> 1), rows g / g + 8
+    const int ch0 = 2 * (8 * (2 * (t & 1) + (t >> 1)) + g), ch1 = ch0 + 1;
+    if (threadIdx.x < 32) {
+        s_ew[lane][0] = make_float4(W(0, ch0), W(1, ch0), -W(kf, ch0), -W(kf + 1, ch0));
+        s_ew[lane][1] = make_float4(-W(kf + 2, ch0), __ldg(a.bias + ch0), W(0, ch1), W(1, ch1));
+        s_ew[lane][2] = make_float4(-W(kf, ch1), -W(kf + 1, ch1), -W(kf + 2, ch1), __ldg(a.bias + ch1));
     }
-    // the two channels this lane finalises
-    const int ch0 = 8 * g + 2 * t, ch1 = ch0 + 1;
-    const float wx0 = W(0, ch0), wx1 = W(0, ch1), wy0 = W(1, ch0), wy1 = W(1, ch1);
-    const float wmx0 = W(kf, ch0), wmx1 = W(kf, ch1), wmy0 = W(kf + 1, ch0), wmy1 = W(kf + 1, ch1);
-    const float wmz0 = W(kf + 2, ch0), wmz1 = W(kf + 2, ch1);
-    const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
-    const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
+    for (int i = threadIdx.x; i < PFN_RQ; i += PFN_WARPS * 32) {
+        const float rn = __frcp_rn((float)max(i, 1));
+        s_rq[i] = make_float2(rn * a.iq_xy, rn * a.iq_z);
+    }
+    __syncthreads();
     const float qscale = (t < 2) ? a.q_xy : (t == 2 ? a.q_z : 0.0f);
-    const float qoff = (t == 2) ? a.zmid : 0.0f;
+    const float qbias = (t == 2) ? -a.zmid * a.q_z : 0.0f;      // (v - zmid) * q_z as one FMA: zmid * q_z is exact (q_z = 2^k)
     const int cells = a.nx * a.ny;
     const int gsize = 1 << a.gshift;
     const int groups = (cells + gsize - 1) >> a.gshift;
@@ -335,110 +362,118 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 3) pfn_scatter_mma_kernel(cons
         if (grp >= total) break;
         const int b = grp / groups, c0 = (grp - b * groups) << a.gshift;
         const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
-        const float *pts = reinterpret_cast<const float *>(a.sorted + (int64_t)b * a.N);
+        const float *pts = reinterpret_cast<const float *>(a.sorted + (int64_t)b * a.N) + t;
         const int cl = min(c0 + lane, cells);
         const int my_o = __ldg(offc + cl);
         const int my_n = __ldg(offc + min(cl + 1, cells)) - my_o;
         const int ncell = min(gsize, cells - c0);
+        unsigned occ = __ballot_sync(0xffffffffu, lane < ncell && my_n > 0);
+        // first step of the first occupied cell: in flight while the empty cells get their zeros
+        int jc = occ ? __ffs(occ) - 1 : 0;
+        int n = __shfl_sync(0xffffffffu, my_n, jc), o = __shfl_sync(0xffffffffu, my_o, jc);
+        float vnext = occ ? __ldg(pts + 4 * (o + min(g, n - 1))) : 0.0f;
         if (lane < ncell && my_n == 0) {           // empty cells: the owning lane writes the 64 zeros
-            const int64_t o = ((int64_t)b * cells + c0 + lane) * PFN_OUT;
+            const int64_t oz = ((int64_t)b * cells + c0 + lane) * PFN_OUT;
             const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
             if (a.out32) {
 #pragma unroll
-                for (int k = 0; k < 16; ++k) reinterpret_cast<uint4 *>(a.out32 + o)[k] = z4;
+                for (int k = 0; k < 16; ++k) reinterpret_cast<uint4 *>(a.out32 + oz)[k] = z4;
             } else {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_hi + o)[k] = z4;
+                for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_hi + oz)[k] = z4;
                 if (a.out_lo) {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_lo + o)[k] = z4;
+                    for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_lo + oz)[k] = z4;
                 }
             }
         }
+        // :125-126 pillar centre of the lane's own cell: coors * v + offset, two float32 roundings like torch's mul then add
         const int my_cy = cl / a.nx, my_cx = cl - my_cy * a.nx;
-        unsigned occ = __ballot_sync(0xffffffffu, lane < ncell && my_n > 0);
+        const float my_pcx = __fadd_rn(__fmul_rn((float)my_cx, a.vx), a.xoff);
+        const float my_pcy = __fadd_rn(__fmul_rn((float)my_cy, a.vy), a.yoff);
+        const int64_t out0 = ((int64_t)b * cells + c0) * PFN_OUT + ch0;
         while (occ) {
-            const int jc = __ffs(occ) - 1;
             occ &= occ - 1;
-            const int n = __shfl_sync(0xffffffffu, my_n, jc);
-            const int o = __shfl_sync(0xffffffffu, my_o, jc);
-            const int cx = __shfl_sync(0xffffffffu, my_cx, jc), cy = __shfl_sync(0xffffffffu, my_cy, jc);
-            // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
-            const float pcx = __fadd_rn(__fmul_rn((float)cx, a.vx), a.xoff);
-            const float pcy = __fadd_rn(__fmul_rn((float)cy, a.vy), a.yoff);
+            const int cur = jc, n_cur = n;
+            const float *cell_pts = pts + 4 * o;
+            float vraw = vnext;
+            if (occ) {                              // the next occupied cell's first step, ahead of this cell's arithmetic
+                jc = __ffs(occ) - 1;
+                n = __shfl_sync(0xffffffffu, my_n, jc);
+                o = __shfl_sync(0xffffffffu, my_o, jc);
+                vnext = __ldg(pts + 4 * (o + min(g, n - 1)));
+            }
+            const float pcx = __shfl_sync(0xffffffffu, my_pcx, cur), pcy = __shfl_sync(0xffffffffu, my_pcy, cur);
             const float sub = (t == 0) ? pcx : (t == 1 ? pcy : 0.0f);
-            float m[8][2];
+            float m[4][2];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { m[j][0] = -INFINITY; m[j][1] = -INFINITY; }
+            for (int mt = 0; mt < 4; ++mt) { m[mt][0] = -INFINITY; m[mt][1] = -INFINITY; }
             int qsum = 0;
-            const float *cell_pts = pts + (int64_t)o * 4 + t;
-            for (int r0 = 0; r0 < n; r0 += 16) {
-                const int row0 = r0 + g, row1 = row0 + 8;
-                // rows past the end repeat the last point: the maximum does not change, the mean skips them
-                const float v0 = __ldg(cell_pts + 4 * min(row0, n - 1)) - sub;
-                const float v1 = __ldg(cell_pts + 4 * min(row1, n - 1)) - sub;
-                if (row0 < n) qsum += __float2int_rn((v0 - qoff) * qscale);
-                if (row1 < n) qsum += __float2int_rn((v1 - qoff) * qscale);
-                const uint32_t a0 = to_tf32(v0), a1 = to_tf32(v1);
-                const uint32_t a2 = to_tf32(v0 - __uint_as_float(a0)), a3 = to_tf32(v1 - __uint_as_float(a1));
+#pragma unroll 1
+            for (int r0 = 0; r0 < n_cur; r0 += 8) {
+                const int row = r0 + g;
+                // points past the end repeat the last one: the maximum does not change, the mean skips them
+                if (r0) vraw = __ldg(cell_pts + 4 * min(row, n_cur - 1));
+                const float v = vraw - sub;
+                const int q = __float2int_rn(fmaf(v, qscale, qbias));
+                if (row < n_cur) qsum += q;
+                // hi = the value with its low 13 mantissa bits cleared (what the tensor core reads of a 32-bit operand),
+                // lo = the exact remainder (<= 13 significant bits, of which the tensor core keeps 11)
+                const uint32_t bh = __float_as_uint(v) & 0xffffe000u;
+                const uint32_t bl = __float_as_uint(v - __uint_as_float(bh));
+                float c[4][4];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float zero[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-                    float c1[4], c2[4];
-                    mma_tf32_16x8x8(c1, a0, a1, a2, a3, blo[j], 0u, zero);          // hi W'lo (small terms first)
-                    mma_tf32_16x8x8(c2, a0, a1, a2, a3, bhi[j], bhi[j], c1);        // + hi W'hi + lo W'hi
-                    m[j][0] = fmaxf(m[j][0], fmaxf(c2[0], c2[2]));
-                    m[j][1] = fmaxf(m[j][1], fmaxf(c2[1], c2[3]));
+                for (int mt = 0; mt < 4; ++mt) mma_tf32_16x8x4(c[mt], alo[mt][0], alo[mt][1], bh);                 // W'lo hi (small term first)
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt) mma_tf32_16x8x8_acc(c[mt], ahi[mt][0], ahi[mt][1], bh, bl);         // + W'hi hi + W'hi lo
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt) {
+                    m[mt][0] = fmaxf(m[mt][0], fmaxf(c[mt][0], c[mt][1]));
+                    m[mt][1] = fmaxf(m[mt][1], fmaxf(c[mt][2], c[mt][3]));
                 }
             }
-            // feature sums over the 8 row groups (lanes with the same t)
+            // feature sums: the 8 lanes with the same t hold the pieces of feature t
             qsum += __shfl_xor_sync(0xffffffffu, qsum, 4);
             qsum += __shfl_xor_sync(0xffffffffu, qsum, 8);
             qsum += __shfl_xor_sync(0xffffffffu, qsum, 16);
             const int qx = __shfl_sync(0xffffffffu, qsum, 0), qy = __shfl_sync(0xffffffffu, qsum, 1);
             const int qz = __shfl_sync(0xffffffffu, qsum, 2);
-            // maxima: reduce-scatter over the row groups; lane (g, t) ends with tile g, i.e. channels 8 g + 2 t, + 1
-            float r4[4][2], r2[2][2], r1[2];
+            // maxima over the point pairs of the four t lanes: reduce-scatter, lane (g, t) ends with tile 2 (t & 1) + (t >> 1)
+            float r4[2][2], r2[2];
             {
-                const bool low = (g & 4) == 0;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        const float send = low ? m[4 + i][k] : m[i][k];
-                        const float recv = __shfl_xor_sync(0xffffffffu, send, 16);
-                        r4[i][k] = fmaxf(low ? m[i][k] : m[4 + i][k], recv);
-                    }
-            }
-            {
-                const bool low = (g & 2) == 0;
+                const bool low = (t & 1) == 0;
 #pragma unroll
                 for (int i = 0; i < 2; ++i)
 #pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        const float send = low ? r4[2 + i][k] : r4[i][k];
-                        const float recv = __shfl_xor_sync(0xffffffffu, send, 8);
-                        r2[i][k] = fmaxf(low ? r4[i][k] : r4[2 + i][k], recv);
+                    for (int h = 0; h < 2; ++h) {
+                        const float send = low ? m[2 + i][h] : m[i][h];
+                        const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                        r4[i][h] = fmaxf(low ? m[i][h] : m[2 + i][h], recv);
                     }
             }
             {
-                const bool low = (g & 1) == 0;
+                const bool low = (t & 2) == 0;
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const float send = low ? r2[1][k] : r2[0][k];
-                    const float recv = __shfl_xor_sync(0xffffffffu, send, 4);
-                    r1[k] = fmaxf(low ? r2[0][k] : r2[1][k], recv);
+                for (int h = 0; h < 2; ++h) {
+                    const float send = low ? r4[1][h] : r4[0][h];
+                    const float recv = __shfl_xor_sync(0xffffffffu, send, 2);
+                    r2[h] = fmaxf(low ? r4[0][h] : r4[1][h], recv);
                 }
             }
-            const float rn = __frcp_rn((float)n);
-            const float mxr = (float)qx * (rn * a.iq_xy), myr = (float)qy * (rn * a.iq_xy);   // mean(x'), mean(y')
-            const float mz = a.zmid + (float)qz * (rn * a.iq_z);
-            const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(-wmx0, mxr, fmaf(-wmy0, myr, fmaf(-wmz0, mz, b0)))));
-            const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(-wmx1, mxr, fmaf(-wmy1, myr, fmaf(-wmz1, mz, b1)))));
+            float2 rq;
+            if (n_cur < PFN_RQ) rq = s_rq[n_cur];
+            else { const float rn = __frcp_rn((float)n_cur); rq = make_float2(rn * a.iq_xy, rn * a.iq_z); }
+            const float mxr = (float)qx * rq.x, myr = (float)qy * rq.x;      // mean(x'), mean(y')
+            const float mz = fmaf((float)qz, rq.y, a.zmid);
+            const float4 e0 = s_ew[lane][0], e1 = s_ew[lane][1], e2 = s_ew[lane][2];
+            // e0 = (wx0, wy0, -wmx0, -wmy0)  e1 = (-wmz0, b0, wx1, wy1)  e2 = (-wmx1, -wmy1, -wmz1, b1)
+            const float E0 = fmaf(e0.x, pcx, fmaf(e0.y, pcy, fmaf(e0.z, mxr, fmaf(e0.w, myr, fmaf(e1.x, mz, e1.y)))));
+            const float E1 = fmaf(e1.z, pcx, fmaf(e1.w, pcy, fmaf(e2.x, mxr, fmaf(e2.y, myr, fmaf(e2.z, mz, e2.w)))));
             // padded slots give relu(b') (:137-140 then :54-58)
-            const float o0 = fmaxf(r1[0] + E0, n < a.P ? rb0 : 0.0f);
-            const float o1 = fmaxf(r1[1] + E1, n < a.P ? rb1 : 0.0f);
-            const int64_t oidx = ((int64_t)b * cells + c0 + jc) * PFN_OUT + ch0;
+            const bool padded = n_cur < a.P;
+            const float o0 = fmaxf(r2[0] + E0, padded ? fmaxf(e1.y, 0.0f) : 0.0f);
+            const float o1 = fmaxf(r2[1] + E1, padded ? fmaxf(e2.w, 0.0f) : 0.0f);
+            const int64_t oidx = out0 + cur * PFN_OUT;
             if (a.out32) {
                 *reinterpret_cast<float2 *>(a.out32 + oidx) = make_float2(o0, o1);
             } else {
@@ -548,8 +583,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     int blocks = (int)((warps + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 4) blocks = 148 * 4;      // the resident set: work is handed out dynamically
     const bool has_r = ctx->cfg.input_features > 3;
-    if (!ctx->cfg.with_distance && ctx->opt_pfn_path == 0) {      // tensor-core variant (no |p| feature: four regrouped inputs)
-        if (blocks > 148 * 3) blocks = 148 * 3;
+    if (!ctx->cfg.with_distance && ctx->opt_pfn_path == 2) {      // tensor-core variant (no |p| feature: four regrouped inputs)
         if (has_r) pfn_scatter_mma_kernel<true><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
         else pfn_scatter_mma_kernel<false><<<blocks, PFN_WARPS * 32, 0, st>>>(a);
         GND_LAUNCH_CHECK("pfn_scatter_mma_kernel");

@@ -253,7 +253,8 @@ class GroundEstimatorNet(nn.Module):
 
     def set_option(self, name, value):
         """gnd_set_option: "conv_path" (0 CTA-pair halo kernel, 1 single-CTA tap kernel), "conv_geometry" (0 auto, 1
-        throughput, 2 small-batch)."""
+        throughput, 2 small-batch), "pfn_path" (0 auto, 1 CUDA-core, 2 mma.sync), "vox_path" (0 auto, 1 order-exact, 2
+        set-exact): include/gndnet_b200.h."""
         with self._lock:
             self._ensure_ctx()
             _lib.check(_lib.lib().gnd_set_option(self._ctx, name.encode(), int(value)), "gnd_set_option")

@@ -291,8 +291,9 @@ GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
 /* Per-ctx switches (tests, A/B timing; never read from the environment at launch time):
  *   "conv_path"      0 = CTA-pair halo kernel where the shape fits (default), 1 = single-CTA tap kernel (the fallback)
  *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel
- *   "pfn_path"       fused pillar encoder: 0 = mma.sync TF32x3 kernel (default), 1 = CUDA-core kernel (also the one used
- *                    with cfg.with_distance)
+ *   "pfn_path"       fused pillar encoder: 0 = automatic (default; today the CUDA-core kernel: 0.21 ms against 0.24 ms per
+ *                    64 scans), 1 = CUDA-core kernel, 2 = mma.sync TF32x3 kernel (cfg.with_distance == 0 only; else the
+ *                    CUDA-core kernel runs)
  *   "vox_path"       gnd_infer only: 0 = automatic (default): set-exact voxelization -- same coors / num_points /
  *                    voxel_count and the same kept points per pillar, but no slot-ordered point_list / offsets -- unless
  *                    the cloud is dense (more than 32 points per cell on average), 1 = always the order-exact kernels
