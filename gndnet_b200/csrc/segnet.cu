@@ -193,13 +193,38 @@ __global__ void __launch_bounds__(256) pool_mask_h8_kernel(const Act in, const A
     }
 }
 
-// one thread per (2x2 output window incl. partial border windows, 8 channels)
+// one thread per (2x2 output window incl. partial border windows, 8 channels).  MaxUnpool2d only MOVES values
+// (segnet.py:84,89), so the planes are handled as raw 16-bit patterns: the four argmax bytes of a word give two byte
+// masks (bit 0 / bit 1 of every byte, spread by a multiply), their four boolean combinations select the window
+// position, PRMT widens byte masks to half masks.  ~100 instructions per thread against ~520 through float
+// conversions (ncu: the kernel was issue-bound at 3 TB/s).
+__device__ __forceinline__ void unpool_plane(const __half *__restrict__ src, __half *__restrict__ dst, bool have, size_t s,
+                                             size_t r0, size_t r1, int C, uint2 kk, bool w1, bool h1) {
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (have) v = __ldg(reinterpret_cast<const uint4 *>(src + s));
+    const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+    const uint32_t kw[2] = {kk.x, kk.y};
+    uint32_t o[4][4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t m0 = (kw[h] & 0x01010101u) * 0xffu;            // 0xff in every byte whose argmax has bit 0 set
+        const uint32_t m1 = ((kw[h] >> 1) & 0x01010101u) * 0xffu;     // ... bit 1
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const uint32_t bm = ((w & 2) ? m1 : ~m1) & ((w & 1) ? m0 : ~m0);
+            o[w][2 * h] = vv[2 * h] & __byte_perm(bm, 0u, 0x1100);
+            o[w][2 * h + 1] = vv[2 * h + 1] & __byte_perm(bm, 0u, 0x3322);
+        }
+    }
+    *reinterpret_cast<uint4 *>(dst + r0) = make_uint4(o[0][0], o[0][1], o[0][2], o[0][3]);
+    if (w1) *reinterpret_cast<uint4 *>(dst + r0 + C) = make_uint4(o[1][0], o[1][1], o[1][2], o[1][3]);
+    if (h1) *reinterpret_cast<uint4 *>(dst + r1) = make_uint4(o[2][0], o[2][1], o[2][2], o[2][3]);
+    if (h1 && w1) *reinterpret_cast<uint4 *>(dst + r1 + C) = make_uint4(o[3][0], o[3][1], o[3][2], o[3][3]);
+}
+
 __global__ void __launch_bounds__(256) unpool_h8_kernel(const Act in, const uint8_t *idx, const Act out, int B) {
     const int C8 = out.C / 8, H = out.H, W = out.W, Hp = in.H, Wp = in.W, Hc = (H + 1) / 2, Wc = (W + 1) / 2;
     const size_t total = (size_t)B * Hc * Wc * C8;
-    H8 zero;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) zero.v[k] = 0.0f;
     for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
         const int c = (int)(g % C8) * 8;
         size_t p = g / C8;
@@ -209,23 +234,18 @@ __global__ void __launch_bounds__(256) unpool_h8_kernel(const Act in, const uint
         const size_t r0 = (((size_t)b * H + 2 * hc) * W + 2 * wc) * out.C + c;
         const size_t r1 = r0 + (size_t)W * out.C;
         const bool h1 = 2 * hc + 1 < H, w1 = 2 * wc + 1 < W;
-        H8 o0 = zero, o1 = zero, o2 = zero, o3 = zero;
-        if (hc < Hp && wc < Wp) {
-            const size_t s = (((size_t)b * Hp + hc) * Wp + wc) * out.C + c;
-            const H8 v = load_h8(in, s);
-            const uint2 kk = __ldg(reinterpret_cast<const uint2 *>(idx + s));
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const int w = (int)(((k < 4 ? kk.x : kk.y) >> (8 * (k & 3))) & 0xff);
-                if (w == 0) o0.v[k] = v.v[k]; else if (w == 1) o1.v[k] = v.v[k]; else if (w == 2) o2.v[k] = v.v[k]; else o3.v[k] = v.v[k];
-            }
+        const bool have = hc < Hp && wc < Wp;      // floor mode: an odd last row / column is never pooled -> zeros
+        const size_t s = (((size_t)b * Hp + hc) * Wp + wc) * out.C + c;
+        uint2 kk = make_uint2(0u, 0u);
+        if (have) kk = __ldg(reinterpret_cast<const uint2 *>(idx + s));
+        unpool_plane(in.hi, out.hi, have, s, r0, r1, out.C, kk, w1, h1);
+        if (out.lo) {
+            if (in.lo) unpool_plane(in.lo, out.lo, have, s, r0, r1, out.C, kk, w1, h1);
+            else unpool_plane(in.hi, out.lo, false, s, r0, r1, out.C, kk, w1, h1);          // no low part: zeros
         }
-        store_h8(out, r0, o0);
-        if (w1) store_h8(out, r0 + out.C, o1);
-        if (h1) store_h8(out, r1, o2);
-        if (h1 && w1) store_h8(out, r1 + out.C, o3);
     }
 }
+
 
 // ---- strict fp32 convolution: 8x8 pixels x 64 output channels per CTA, 4x4 outputs per thread ----
 __global__ void __launch_bounds__(256) conv3x3_f32_kernel(const float *__restrict__ in, const float *__restrict__ w,
