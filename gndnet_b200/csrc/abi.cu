@@ -65,11 +65,13 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
     int32_t *pfn_ctr = c.take<int32_t>(4);
     double *bn_partial = cfg.bn_batch_stats ? c.take<double>((size_t)BN_BLOCKS * 256 * 2) : nullptr;
     float *bn_ab = cfg.bn_batch_stats ? c.take<float>(512) : nullptr;
+    float *bn_stats = cfg.bn_batch_stats ? c.take<float>(8 * 512) : nullptr;
     if (ws) {
-        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr; ctx->bn_partial = bn_partial; ctx->bn_ab = bn_ab;
+        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr; ctx->bn_partial = bn_partial; ctx->bn_ab = bn_ab; ctx->bn_stats = bn_stats;
         if (names) {
             names->push_back({"idx1", idx1, (size_t)B * H1 * W1 * 128});
             if (regpart) names->push_back({"regpart", regpart, (size_t)B * H * W * 9 * 4});
+            if (bn_stats) names->push_back({"bn_stats", bn_stats, (size_t)8 * 512 * 4});
             names->push_back({"coors", coors, (size_t)B * mv * 3 * 4});
             names->push_back({"num_points", num, (size_t)B * mv * 4});
             names->push_back({"voxel_count", cnt, (size_t)B * 4});

@@ -70,6 +70,7 @@ struct gnd_ctx {
     float *regpart = nullptr;  // [B][H][W][9] per-tap regressor partials (tcgen05 modes)
     double *bn_partial = nullptr;   // [BN_BLOCKS][256][2] per-block channel sums (batch-statistics mode)
     float *bn_ab = nullptr;         // [2][256] per-channel scale / shift of the current layer
+    float *bn_stats = nullptr;      // [8][256][2] batch mean / unbiased variance of every conv block (bn_batch_stats)
     int32_t *pfn_ctr = nullptr; // [2] work-queue head + finished-CTA count of pfn_scatter_kernel (self-resetting)
     gnd::TensorMaps *tmaps = nullptr;
     gnd::Halo2Maps *h2maps = nullptr;

@@ -395,8 +395,10 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const float *__restrict
     }
 }
 
+// `stats` [C][2]: the batch mean and the UNBIASED variance, what nn.BatchNorm2d in training mode blends into its
+// running buffers (momentum 0.1) -- the host side applies that update (gndnet_b200.model, bn_mode="batch").
 __global__ void bn_final_kernel(const double *partial, int nblk, int64_t npix, const float *gamma, const float *beta,
-                                float *ab) {
+                                float *ab, float *stats) {
     const int c = threadIdx.x;
     double s = 0.0, q = 0.0;
     for (int b = 0; b < nblk; ++b) { s += partial[((size_t)b * 256 + c) * 2]; q += partial[((size_t)b * 256 + c) * 2 + 1]; }
@@ -406,6 +408,10 @@ __global__ void bn_final_kernel(const double *partial, int nblk, int64_t npix, c
     const double alpha = (double)gamma[c] / sqrt(var + 1e-5);
     ab[c] = (float)alpha;
     ab[256 + c] = (float)((double)beta[c] - mean * alpha);
+    if (stats) {
+        stats[2 * c] = (float)mean;
+        stats[2 * c + 1] = (float)(npix > 1 ? var * ((double)npix / (double)(npix - 1)) : var);
+    }
 }
 
 __global__ void __launch_bounds__(256) bn_apply_relu_kernel(float *x, int64_t n4, int C, const float *__restrict__ ab) {
@@ -433,7 +439,8 @@ static int conv_f32(gnd_ctx *ctx, int layer, const Act &in, const Act &out, int 
         if (nblk > BN_BLOCKS) nblk = BN_BLOCKS;
         bn_partial_kernel<<<nblk, 256, 0, st>>>(out.f32, npix, L.cout, ctx->bn_partial);
         GND_LAUNCH_CHECK("bn_partial_kernel");
-        bn_final_kernel<<<1, L.cout, 0, st>>>(ctx->bn_partial, nblk, npix, L.gamma, L.beta, ctx->bn_ab);
+        bn_final_kernel<<<1, L.cout, 0, st>>>(ctx->bn_partial, nblk, npix, L.gamma, L.beta, ctx->bn_ab,
+                                              ctx->bn_stats ? ctx->bn_stats + (size_t)layer * 512 : nullptr);
         GND_LAUNCH_CHECK("bn_final_kernel");
         const int64_t n4 = npix * L.cout / 4;
         bn_apply_relu_kernel<<<ew_blocks((size_t)n4), 256, 0, st>>>(out.f32, n4, L.cout, ctx->bn_ab);

@@ -96,11 +96,15 @@ class SegnetGndEst(nn.Module):
 
 
 class GroundEstimatorNet(nn.Module):
-    def __init__(self, cfg, precision=None, bn_mode="running"):
+    def __init__(self, cfg, precision=None, bn_mode="running", update_running_stats=True):
         """``bn_mode``: "running" (default) evaluates every BatchNorm2d with its running statistics, i.e. the module
         after ``.eval()`` as the deployed node runs it (ros_node.py:227); "batch" reproduces the module left in
         TRAINING mode -- statistics of the batch in flight -- which is what predict_ground.py computes because it
-        never calls ``.eval()``.  "batch" needs ``precision="fp32"``; running buffers are not updated."""
+        never calls ``.eval()``.  "batch" needs ``precision="fp32"``.  Like the reference in training
+        mode (modules/segnet.py:35-38: nn.BatchNorm2d, momentum 0.1), every forward / infer in "batch" mode then blends
+        the batch mean and unbiased variance into ``running_mean`` / ``running_var`` and counts ``num_batches_tracked``,
+        so ``state_dict()`` after k forwards equals the reference's; ``update_running_stats=False`` leaves the buffers
+        alone."""
         super().__init__()
         self.cfg = cfg
         self.precision = precision or getattr(cfg, "precision", "mixed")
@@ -111,6 +115,7 @@ class GroundEstimatorNet(nn.Module):
         if bn_mode == "batch" and self.precision != "fp32":
             raise ValueError('bn_mode="batch" needs precision="fp32"')
         self.bn_mode = bn_mode
+        self.update_running_stats = bool(update_running_stats)
         self.voxel_feature_extractor = PillarFeatureNet(
             num_input_features=cfg.input_features, use_norm=cfg.use_norm, num_filters=cfg.vfe_filters,
             with_distance=cfg.with_distance, voxel_size=cfg.voxel_size, pc_range=cfg.pc_range)
@@ -171,7 +176,9 @@ class GroundEstimatorNet(nn.Module):
         # load_state_dict(assign=True), re-assigned Parameters and dtype / device moves.  ~60 dict lookups, a few
         # microseconds -- it sits on the batch-1 latency path (state_dict() here cost ~75 us per call).
         if self._slots is None:
-            self._slots = [(d, n) for m in self.modules() for d in (m._parameters, m._buffers) for n in d]
+            # batch-statistics mode never reads the BatchNorm2d running buffers (and updates them after every call)
+            skip = (lambda m, d: self.bn_mode == "batch" and isinstance(m, nn.BatchNorm2d) and d is m._buffers)
+            self._slots = [(d, n) for m in self.modules() for d in (m._parameters, m._buffers) for n in d if not skip(m, d)]
         return tuple((id(t), t._version) for t in (d[n] for d, n in self._slots) if t is not None)
 
     def _ensure_ctx(self, defer_version_check=False):
@@ -277,6 +284,24 @@ class GroundEstimatorNet(nn.Module):
                           'construct with bn_mode="batch", precision="fp32" to reproduce the training-mode arithmetic')
             self._warned_train = True
 
+    def _bn2d_modules(self):
+        ed = self.encoder_decoder
+        return [blk.cbr_unit[1] for blk in (ed.down1.conv1, ed.down1.conv2, ed.down2.conv1, ed.down2.conv2,
+                                            ed.up2.conv1, ed.up2.conv2, ed.up1.conv1, ed.up1.conv2)]
+
+    def _blend_running_stats(self):
+        """nn.BatchNorm2d's training-mode side effect (momentum update with the batch mean / unbiased variance the
+        kernels left in "bn_stats"), enqueued on the current stream behind the forward."""
+        if self.bn_mode != "batch" or not self.update_running_stats:
+            return
+        stats = self.buffer("bn_stats", torch.float32, (8, 256, 2))
+        with torch.no_grad():
+            for l, bn in enumerate(self._bn2d_modules()):
+                C, mom = bn.num_features, (0.1 if bn.momentum is None else bn.momentum)
+                bn.running_mean.mul_(1.0 - mom).add_(stats[l, :C, 0], alpha=mom)
+                bn.running_var.mul_(1.0 - mom).add_(stats[l, :C, 1], alpha=mom)
+                bn.num_batches_tracked.add_(1)
+
     def buffer(self, name, dtype, shape=None):
         """Test / profiling hook: a workspace buffer as a tensor view (gnd_get_buffer)."""
         L = _lib.lib()
@@ -319,6 +344,7 @@ class GroundEstimatorNet(nn.Module):
             n1 = self.last_launch_count()
             _lib.check(L.gnd_segnet(ctx, B, _lib.ptr(height), st), "gnd_segnet")
             self.launches = n1 + self.last_launch_count()
+            self._blend_running_stats()
         return torch.squeeze(height)
 
     # ------------------------------------------------------------------ fused path
@@ -381,6 +407,7 @@ class GroundEstimatorNet(nn.Module):
                 if not self._weights_stale():         # checked behind the launches; a changed parameter re-runs once
                     break
             self.launches = self.last_launch_count()
+            self._blend_running_stats()
         if single:
             return height[0], (lab[0] if lab is not None else None)
         return height, lab

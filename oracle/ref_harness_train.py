@@ -51,7 +51,21 @@ def main():
         print("%-8s %-40s |reference(train) - oracle(batch stats)| = %.3g   (train vs eval output differ by %.3g)" %
               (cfgname, "+".join(names), d, float((o_out - o_eval).abs().max())))
         assert d <= 1e-5, d
-        out[cfgname + "__" + "_".join(names)] = o_out.numpy().astype(np.float32)
+        key = cfgname + "__" + "_".join(names)
+        out[key] = o_out.numpy().astype(np.float32)
+        # the training-mode side effect: running buffers of the eight BatchNorm2d after this ONE forward (momentum 0.1,
+        # unbiased batch variance), straight from the reference module
+        rsd = ref.state_dict()
+        bn = ["down1.conv1", "down1.conv2", "down2.conv1", "down2.conv2", "up2.conv1", "up2.conv2", "up1.conv1", "up1.conv2"]
+        rm = np.zeros((8, 256), np.float32); rv = np.zeros((8, 256), np.float32)
+        for l, nm in enumerate(bn):
+            m = rsd["encoder_decoder.%s.cbr_unit.1.running_mean" % nm].numpy()
+            v2 = rsd["encoder_decoder.%s.cbr_unit.1.running_var" % nm].numpy()
+            rm[l, :len(m)] = m; rv[l, :len(v2)] = v2
+            k0 = "encoder_decoder.%s.cbr_unit.1.num_batches_tracked" % nm
+            assert int(rsd[k0]) == int(np.asarray(sd.get(k0, 0))) + 1
+        out[key + "__running_mean"] = rm
+        out[key + "__running_var"] = rv
     if args.write:
         np.savez_compressed(os.path.join(GOLDEN, "model_heights_train.npz"), **out)
         print("wrote tests/golden/model_heights_train.npz")

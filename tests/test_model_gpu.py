@@ -267,7 +267,33 @@ def test_batch_statistics_batchnorm_matches_train_mode_reference(cfgname, scans,
     helpers.assert_heights(helpers.compare_heights(model, out, ref, st), "fp32", st, "batch-stat BN " + key)
     with np.load(cases.GOLDEN + "/model_heights_train.npz") as z:
         gold = torch.from_numpy(z[key]).reshape(ref.shape)
+        g_mean, g_var = z[key + "__running_mean"], z[key + "__running_var"]
     assert (gold - ref).abs().max().item() <= 2e-5, "oracle (batch statistics) drifted from the reference golden"
+    # the training-mode side effect (segnet.py:35-38, momentum 0.1): running buffers after this one forward equal the
+    # reference module's, and the weights are NOT re-uploaded because of it (the buffers are not kernel inputs here)
+    for l, bn in enumerate(model._bn2d_modules()):
+        C = bn.num_features
+        k0 = "encoder_decoder.%s.cbr_unit.1." % ["down1.conv1", "down1.conv2", "down2.conv1", "down2.conv2", "up2.conv1",
+                                                   "up2.conv2", "up1.conv1", "up1.conv2"][l]
+        dm = np.abs(bn.running_mean.cpu().numpy() - g_mean[l, :C]).max()
+        dv = np.abs(bn.running_var.cpu().numpy() - g_var[l, :C]).max()
+        # (2e-4: blocks behind a max-pool inherit its argmax near-tie flips -- one moved activation shifts a channel's
+        #  batch variance by ~1e-5 on the single 50x50 camera map; the encoder blocks agree to 1e-6)
+        assert dm <= 2e-4 * max(1.0, np.abs(g_mean[l, :C]).max()), "running_mean of block %d differs by %g" % (l, dm)
+        assert dv <= 2e-4 * max(1.0, np.abs(g_var[l, :C]).max()), "running_var of block %d differs by %g" % (l, dv)
+        assert int(bn.num_batches_tracked) == int(np.asarray(sd[k0 + "num_batches_tracked"])) + 1
+    ver = model._weights_version
+    with torch.no_grad():
+        out2 = model(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
+    assert model._weights_version == ver and torch.equal(out, out2)          # batch statistics: the same batch, the same map
+    frozen = GroundEstimatorNet(cfg, precision="fp32", bn_mode="batch", update_running_stats=False)
+    frozen.load_state_dict({k: torch.from_numpy(np.asarray(v_)) for k, v_ in sd.items()}, strict=True)
+    frozen = frozen.to(cuda)
+    with torch.no_grad():
+        out3 = frozen(torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(n).cuda())
+    assert torch.equal(out, out3)
+    assert np.array_equal(frozen._bn2d_modules()[0].running_mean.cpu().numpy(),
+                          np.asarray(sd["encoder_decoder.down1.conv1.cbr_unit.1.running_mean"], dtype=np.float32))
     # and it is a different function from the eval-mode one
     ref_eval = model_ref.forward(sd, cfg, v, c, n)
     assert (ref_eval - ref).abs().max().item() > 1e-2
