@@ -89,7 +89,7 @@ class ScanStream:
 
 
 class GraphedInfer:
-    """The fused path (gnd_infer: ~17 kernels) captured once into a CUDA graph and replayed per scan batch.
+    """The fused path (gnd_infer: 19 kernels) captured once into a CUDA graph and replayed per scan batch.
 
     For the batch-1 latency case (BASELINE.json configs[1]; ros_node.py's one-cloud-at-a-time loop) the launch
     overhead of 17 back-to-back enqueues is a third of the device time; a replay is one launch.  The graph is
