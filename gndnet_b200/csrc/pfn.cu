@@ -120,6 +120,30 @@ __device__ __forceinline__ void pfn_pillar(const PfnArgs &a, int lane, float (*s
     }
 }
 
+// Zeros for the empty cells of a work unit (about half of a LiDAR BEV grid), written by the whole warp: the unit's
+// cells are contiguous in every plane, so lane l stores the 16-byte piece l (+ 32, + 64, ...) of the unit's rows when the
+// cell that piece belongs to is empty -- a handful of fully coalesced store instructions per unit instead of 16 per
+// empty cell from single lanes.
+__device__ __forceinline__ void zero_empty_cells(const PfnArgs &a, int64_t cell0, int ncell, unsigned empty, int lane) {
+    if (!empty) return;
+    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+    if (a.out32) {
+        const int per = PFN_OUT * 4 / 16;                       // 16-byte pieces per cell
+        uint4 *dst = reinterpret_cast<uint4 *>(a.out32 + cell0 * PFN_OUT);
+        for (int i = lane; i < ncell * per; i += 32)
+            if ((empty >> (i / per)) & 1u) dst[i] = z4;
+    } else {
+        const int per = PFN_OUT * 2 / 16;
+        uint4 *dh = reinterpret_cast<uint4 *>(a.out_hi + cell0 * PFN_OUT);
+        uint4 *dl = a.out_lo ? reinterpret_cast<uint4 *>(a.out_lo + cell0 * PFN_OUT) : nullptr;
+        for (int i = lane; i < ncell * per; i += 32)
+            if ((empty >> (i / per)) & 1u) {
+                dh[i] = z4;
+                if (dl) dl[i] = z4;
+            }
+    }
+}
+
 // Fused path: the voxelizer left the kept points grouped by CELL (`sorted`, CSR `offc`), z already shifted.
 // One warp walks 32 consecutive cells; lane l owns channels 2l, 2l+1.  The Linear is regrouped around the
 // pillar centre so that a point costs 4 multiply-adds per channel instead of 9:
@@ -170,21 +194,7 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
         const int ncell = min(gsize, cells - c0);
         // empty cells (about half of a LiDAR BEV grid): the lane that owns the cell writes its 64 zeros with 16-byte
         // stores, once per group, instead of the whole warp walking through the cell
-        if (lane < ncell && my_n == 0) {
-            const int64_t o = ((int64_t)b * cells + c0 + lane) * PFN_OUT;
-            const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-            if (a.out32) {
-#pragma unroll
-                for (int k = 0; k < 16; ++k) reinterpret_cast<uint4 *>(a.out32 + o)[k] = z4;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_hi + o)[k] = z4;
-                if (a.out_lo) {
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_lo + o)[k] = z4;
-                }
-            }
-        }
+        zero_empty_cells(a, (int64_t)b * cells + c0, ncell, __ballot_sync(0xffffffffu, lane < ncell && my_n == 0), lane);
         const int my_cy = cl / a.nx, my_cx = cl - my_cy * a.nx;
         unsigned occ = __ballot_sync(0xffffffffu, lane < ncell && my_n > 0);
         while (occ) {
@@ -372,21 +382,7 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_mma_kernel(cons
         int jc = occ ? __ffs(occ) - 1 : 0;
         int n = __shfl_sync(0xffffffffu, my_n, jc), o = __shfl_sync(0xffffffffu, my_o, jc);
         float vnext = occ ? __ldg(pts + 4 * (o + min(g, n - 1))) : 0.0f;
-        if (lane < ncell && my_n == 0) {           // empty cells: the owning lane writes the 64 zeros
-            const int64_t oz = ((int64_t)b * cells + c0 + lane) * PFN_OUT;
-            const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-            if (a.out32) {
-#pragma unroll
-                for (int k = 0; k < 16; ++k) reinterpret_cast<uint4 *>(a.out32 + oz)[k] = z4;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_hi + oz)[k] = z4;
-                if (a.out_lo) {
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) reinterpret_cast<uint4 *>(a.out_lo + oz)[k] = z4;
-                }
-            }
-        }
+        zero_empty_cells(a, (int64_t)b * cells + c0, ncell, __ballot_sync(0xffffffffu, lane < ncell && my_n == 0), lane);
         // :125-126 pillar centre of the lane's own cell: coors * v + offset, two float32 roundings like torch's mul then add
         const int my_cy = cl / a.nx, my_cx = cl - my_cy * a.nx;
         const float my_pcx = __fadd_rn(__fmul_rn((float)my_cx, a.vx), a.xoff);
@@ -412,9 +408,11 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_mma_kernel(cons
 #pragma unroll 1
             for (int r0 = 0; r0 < n_cur; r0 += 8) {
                 const int row = r0 + g;
-                // points past the end repeat the last one: the maximum does not change, the mean skips them
-                if (r0) vraw = __ldg(cell_pts + 4 * min(row, n_cur - 1));
+                // points past the end repeat the last one: the maximum does not change, the mean skips them.  The next
+                // step's row is requested before this step's arithmetic (one load in flight across the MMA chain)
+                const float vahead = (r0 + 8 < n_cur) ? __ldg(cell_pts + 4 * min(row + 8, n_cur - 1)) : 0.0f;
                 const float v = vraw - sub;
+                vraw = vahead;
                 const int q = __float2int_rn(fmaf(v, qscale, qbias));
                 if (row < n_cur) qsum += q;
                 // hi = the value with its low 13 mantissa bits cleared (what the tensor core reads of a 32-bit operand),
