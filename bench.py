@@ -397,25 +397,6 @@ def h2d_probe(pinned, dev_buf, seconds=0.25):
     return reps * nbytes / 1e6 / a.elapsed_time(b)
 
 
-def rate_shards(rates, total, lo, hi):
-    """Split `total` scans over the ranks in proportion to their link rates (largest-remainder), each within [lo, hi]."""
-    r = np.asarray(rates, dtype=np.float64)
-    want = np.clip(total * r / r.sum(), lo, hi)
-    want *= total / want.sum()
-    base = np.clip(np.floor(want).astype(int), lo, hi)
-    rem = total - int(base.sum())
-    order = np.argsort(-(want - base))
-    i = 0
-    while rem != 0 and i < 10 * len(r):
-        k = order[i % len(r)]
-        step = 1 if rem > 0 else -1
-        if lo <= base[k] + step <= hi:
-            base[k] += step
-            rem -= step
-        i += 1
-    return [int(x) for x in base]
-
-
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -449,7 +430,7 @@ def main():
     import torch.distributed as dist
     from gndnet_b200 import synth
     from gndnet_b200.model import GroundEstimatorNet
-    from gndnet_b200.pipeline import ScanStream, GraphedInfer, shard_range, max_over_ranks
+    from gndnet_b200.pipeline import ScanStream, GraphedInfer, shard_range, max_over_ranks, rate_shards, gather_rates
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: there is no CPU fallback"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -486,12 +467,7 @@ def main():
         dist.barrier()
     my_rate = h2d_probe(pinned[0][:B], probe_buf)
     del probe_buf
-    rates = [my_rate]
-    if world > 1:
-        t = torch.tensor([my_rate], dtype=torch.float64, device=dev)
-        allr = [torch.zeros_like(t) for _ in range(world)]
-        dist.all_gather(allr, t)
-        rates = [float(x.item()) for x in allr]
+    rates = gather_rates(my_rate, device=dev)
     shards = [B] * world if (world == 1 or args.equal_shards) else rate_shards(rates, world * B, max(8, B // 2), Bmax)
     my_b = shards[rank]
     pipe = ScanStream(model, Bmax, N_POINTS, depth=2, labels="int8", threshold=0.08, split=max(1, args.split))
@@ -571,10 +547,7 @@ def main():
                 pipe.drain()
                 c1.record()
                 torch.cuda.synchronize()
-            t = torch.tensor([my_b * 8 / c0.elapsed_time(c1)], dtype=torch.float64, device=dev)
-            allr = [torch.zeros_like(t) for _ in range(world)]
-            dist.all_gather(allr, t)
-            shards = rate_shards([float(x.item()) for x in allr], world * B, max(8, B // 2), Bmax)
+            shards = rate_shards(gather_rates(my_b * 8 / c0.elapsed_time(c1), device=dev), world * B, max(8, B // 2), Bmax)
             my_b = shards[rank]
             shard_history.append(list(shards))
     ms_e2e, ms_e2e_own, _, soak_e = timed(step_e2e, args.steps, args.warmup, after=pipe.drain)

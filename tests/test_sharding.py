@@ -8,7 +8,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from gndnet_b200.pipeline import gather_shard_sizes, max_over_ranks, shard_range
+from gndnet_b200.pipeline import gather_rates, gather_shard_sizes, max_over_ranks, rate_shards, shard_range
 
 
 def test_shard_range_partitions_exactly():
@@ -23,6 +23,21 @@ def test_shard_range_partitions_exactly():
         shard_range(8, 2, 2)
 
 
+def test_rate_shards_follow_the_link_rates():
+    # the measured 8-GPU box: 20.5 GB/s to GPUs 0-3, 36 GB/s to GPUs 4-7
+    s = rate_shards([20.5] * 4 + [36.0] * 4, 512, 32, 128)
+    assert sum(s) == 512 and max(s[:4]) - min(s[:4]) <= 1 and max(s[4:]) - min(s[4:]) <= 1 and s[0] in (46, 47) and s[4] in (81, 82)
+    assert abs(s[0] / s[4] - 20.5 / 36.0) < 0.02
+    assert rate_shards([55.4, 55.4], 128, 32, 128) == [64, 64]           # equal links: equal shards
+    assert rate_shards([1.0, 100.0], 128, 32, 128) == [32, 96]           # the bounds hold
+    assert rate_shards([3.0], 64, 8, 128) == [64]
+    for bad in ([], [1.0, 0.0], [1.0, float("nan")]):
+        with pytest.raises(ValueError):
+            rate_shards(bad, 128, 32, 128)
+    with pytest.raises(ValueError):
+        rate_shards([1.0, 1.0], 300, 32, 128)
+
+
 def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -30,6 +45,9 @@ def _worker(rank, world, port, q):
         lo, hi = shard_range(129, rank, world)
         sizes = gather_shard_sizes(hi - lo)
         ms = max_over_ranks(10.0 + 5.0 * rank)
+        # link-rate-proportional e2e shards: every rank gathers the rates and computes the same split
+        shards = rate_shards(gather_rates(20.0 + 16.0 * rank), 128, 32, 128)
+        assert sum(shards) == 128 and shards == [46, 82], shards
         # every scan is owned by exactly one rank: gather the ownership masks
         own = torch.zeros(129, dtype=torch.int32)
         own[lo:hi] = 1
