@@ -375,11 +375,12 @@ def run_reference(args, rank):
 
 
 # ---------------------------------------------------------------------------------------------- host link
-def h2d_probe(pinned, dev_buf, seconds=0.25):
+def h2d_probe(pinned, dev_buf, seconds=0.25, d2h=None):
     """Pinned host -> device copy rate of THIS rank's link, GB/s (all ranks call it at the same time, so the figure is
-    the rate under the same contention the e2e run sees)."""
+    the rate under the same contention the e2e run sees).  ``d2h`` = (device tensor, pinned host tensor): the step's
+    result read-back runs next to every copy on a second stream, i.e. the run's own traffic mix."""
     import torch
-    s = torch.cuda.Stream()
+    s, s2 = torch.cuda.Stream(), torch.cuda.Stream()
     nbytes = pinned.numel() * pinned.element_size()
     with torch.cuda.stream(s):
         dev_buf.copy_(pinned, non_blocking=True)
@@ -389,11 +390,15 @@ def h2d_probe(pinned, dev_buf, seconds=0.25):
         a.record()
         while time.perf_counter() - t0 < seconds:
             dev_buf.copy_(pinned, non_blocking=True)
+            if d2h is not None:
+                with torch.cuda.stream(s2):
+                    d2h[1].copy_(d2h[0], non_blocking=True)
             reps += 1
             if reps % 4 == 0:
                 s.synchronize()
         b.record()
         s.synchronize()
+        s2.synchronize()
     return reps * nbytes / 1e6 / a.elapsed_time(b)
 
 
@@ -466,7 +471,15 @@ def main():
     if world > 1:
         dist.barrier()
     my_rate = h2d_probe(pinned[0][:B], probe_buf)
-    del probe_buf
+    rates_h2d_only = gather_rates(my_rate, device=dev)
+    # ... and next to the run's own device -> host traffic (labels + height maps of the same batch): the ceiling e2e is
+    # quoted against, and the rates the shards follow
+    d2h_src = torch.empty(B * (N_POINTS + model.ny * model.nx * 4), dtype=torch.uint8, device=dev)
+    d2h_dst = torch.empty(d2h_src.numel(), dtype=torch.uint8).pin_memory()
+    if world > 1:
+        dist.barrier()
+    my_rate = h2d_probe(pinned[0][:B], probe_buf, d2h=(d2h_src, d2h_dst))
+    del probe_buf, d2h_src, d2h_dst
     rates = gather_rates(my_rate, device=dev)
     shards = [B] * world if (world == 1 or args.equal_shards) else rate_shards(rates, world * B, max(8, B // 2), Bmax)
     my_b = shards[rank]
@@ -724,10 +737,13 @@ def main():
                         "shard_history": shard_history,
                         "h2d_gbs_probe_per_rank": [round(r, 2) for r in rates],
                         "h2d_gbs_in_run_per_rank": [round(r, 2) for r in run_gbs],
+                        "h2d_gbs_probe_h2d_only_per_rank": [round(r, 2) for r in rates_h2d_only],
                         "link_ceiling_scans_s": link_ceiling,
                         "frac_of_link_ceiling": e2e / link_ceiling,
                         "link_note": "ceiling = sum over ranks of the pinned host->device rate measured in this run with all "
-                                     "ranks copying at once, / %d bytes per scan; no kernel can feed host-resident scans faster" % SCAN_BYTES},
+                                     "ranks copying at once NEXT TO the step's device->host read-back (h2d_gbs_probe_per_rank; "
+                                     "the h2d-only probe is printed beside it), / %d bytes per scan; no kernel can feed "
+                                     "host-resident scans faster" % SCAN_BYTES},
                 "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
                 "clocks": clocks}
         line.update(extra)
