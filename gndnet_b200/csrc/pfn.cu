@@ -53,6 +53,7 @@ struct PfnArgs {
 
 constexpr int PFN_WARPS = 8;
 constexpr int FEAT_STRIDE = 12;
+constexpr int PFN_RQ = 128;          // reciprocal table: 1 / n for n < PFN_RQ (max_points_voxel is 100 in every shipped config)
 
 __device__ __forceinline__ void store_cell(const PfnArgs &a, int64_t cell_global, int lane, float m0, float m1) {
     const int64_t o = cell_global * PFN_OUT + 2 * lane;
@@ -160,6 +161,12 @@ template <bool DIST, bool HAS_R>
 __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const PfnArgs a) {
     __shared__ float4 s_pt[PFN_WARPS][32];
     __shared__ float s_dist[PFN_WARPS][32];
+    __shared__ float2 s_rq[PFN_RQ];                // (1/n) * iq_xy, (1/n) * iq_z: one LDS instead of an IEEE reciprocal per cell
+    for (int i = threadIdx.x; i < PFN_RQ; i += PFN_WARPS * 32) {
+        const float rn = __frcp_rn((float)max(i, 1));
+        s_rq[i] = make_float2(rn * a.iq_xy, rn * a.iq_z);
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kf = HAS_R ? 4 : 3;
     auto W = [&](int k, int ch) { return __ldg(a.w + k * PFN_OUT + ch); };
@@ -195,20 +202,21 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
         // empty cells (about half of a LiDAR BEV grid): the lane that owns the cell writes its 64 zeros with 16-byte
         // stores, once per group, instead of the whole warp walking through the cell
         zero_empty_cells(a, (int64_t)b * cells + c0, ncell, __ballot_sync(0xffffffffu, lane < ncell && my_n == 0), lane);
+        // :125-126 pillar centre of the lane's own cell: coors * v + offset, two float32 roundings like torch's mul then add
         const int my_cy = cl / a.nx, my_cx = cl - my_cy * a.nx;
+        const float my_pcx = __fadd_rn(__fmul_rn((float)my_cx, a.vx), a.xoff);
+        const float my_pcy = __fadd_rn(__fmul_rn((float)my_cy, a.vy), a.yoff);
+        const int64_t out0 = ((int64_t)b * cells + c0) * PFN_OUT + 2 * lane;
         unsigned occ = __ballot_sync(0xffffffffu, lane < ncell && my_n > 0);
         while (occ) {
             const int j = __ffs(occ) - 1;
             occ &= occ - 1;
             const int n = __shfl_sync(0xffffffffu, my_n, j);
-            const int cx = __shfl_sync(0xffffffffu, my_cx, j), cy = __shfl_sync(0xffffffffu, my_cy, j);
-            const int64_t oidx = ((int64_t)b * cells + c0 + j) * PFN_OUT + 2 * lane;
+            const int64_t oidx = out0 + j * PFN_OUT;
             float m0 = 0.0f, m1 = 0.0f;
             {
                 const int o = __shfl_sync(0xffffffffu, my_o, j);
-                // :125-126 pillar centre: coors * v + offset, two float32 roundings like torch's mul then add
-                const float pcx = __fadd_rn(__fmul_rn((float)cx, a.vx), a.xoff);
-                const float pcy = __fadd_rn(__fmul_rn((float)cy, a.vy), a.yoff);
+                const float pcx = __shfl_sync(0xffffffffu, my_pcx, j), pcy = __shfl_sync(0xffffffffu, my_pcy, j);
                 float4 p0 = make_float4(pcx, pcy, a.zmid, 0.f);
                 if (lane < n) p0 = __ldg(pts + o + lane);
                 const float4 f0 = make_float4(p0.x - pcx, p0.y - pcy, p0.z, p0.w);
@@ -221,9 +229,11 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
                 qx = __reduce_add_sync(0xffffffffu, qx);
                 qy = __reduce_add_sync(0xffffffffu, qy);
                 qz = __reduce_add_sync(0xffffffffu, qz);
-                const float rn = __frcp_rn((float)n);
-                const float mxr = (float)qx * (rn * a.iq_xy), myr = (float)qy * (rn * a.iq_xy);   // mean(x') , mean(y')
-                const float mz = a.zmid + (float)qz * (rn * a.iq_z);
+                float2 rq;
+                if (n < PFN_RQ) rq = s_rq[n];
+                else { const float rn = __frcp_rn((float)n); rq = make_float2(rn * a.iq_xy, rn * a.iq_z); }
+                const float mxr = (float)qx * rq.x, myr = (float)qy * rq.x;   // mean(x') , mean(y')
+                const float mz = a.zmid + (float)qz * rq.y;
                 const float E0 = fmaf(wx0, pcx, fmaf(wy0, pcy, fmaf(-wmx0, mxr, fmaf(-wmy0, myr, fmaf(-wmz0, mz, b0)))));
                 const float E1 = fmaf(wx1, pcx, fmaf(wy1, pcy, fmaf(-wmx1, mxr, fmaf(-wmy1, myr, fmaf(-wmz1, mz, b1)))));
                 float t0 = -INFINITY, t1 = -INFINITY;
@@ -245,6 +255,8 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
                             t1 = fmaxf(t1, fmaf(G1, dq, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x)))));
                         }
                     } else {
+                        // (pairing two points per step so that the maximum is one FMNMX3 per channel was measured: 0.215 ms
+                        //  against 0.207 ms for this form)
 #pragma unroll 4
                         for (int q = 0; q < cnt; ++q) {
                             const float4 f = s_pt[warp][q];
@@ -320,8 +332,6 @@ __device__ __forceinline__ void mma_tf32_16x8x8_acc(float (&d)[4], uint32_t a0, 
     asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%4,%5}, {%6,%7}, {%0,%1,%2,%3};"
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
 }
-
-constexpr int PFN_RQ = 128;          // reciprocal table: 1 / n for n < PFN_RQ (max_points_voxel is 100 in every shipped config)
 
 template <bool HAS_R>
 __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_mma_kernel(const PfnArgs a) {
