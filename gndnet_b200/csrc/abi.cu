@@ -324,11 +324,12 @@ extern "C" int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *count
     }
     // the fused path needs per cell the SET of kept points, not the slot-ordered index lists: set-exact kernels
     // (voxelize.cu); gnd_voxelize / gnd_points_to_voxel keep producing the lists with the order-exact ones
-    // ... unless the cloud is dense (the camera frames: ~400 points in every cell, all over-full): there the candidate
-    // lists hold every point and the in-order ranking kernels are the cheaper way (measured at 8 x 1 M points:
-    // 0.36 ms set-exact against 0.29 ms order-exact)
+    // ... unless the cloud is dense (the camera frames: ~400 points in every cell, all over-full) AND the batch is small:
+    // measured with 1 M-point frames, order-exact against set-exact (chunked counts): 0.077 / 0.085 ms at batch 1,
+    // 0.147 / 0.183 at 4, 0.264 / 0.270 at 8, 2.03 / 1.61 at 64
+    const bool dense = n_points > (int64_t)32 * ctx->vplan.cells;
     if (ctx->vplan.lean_ok && ctx->vws.lfirst && ctx->opt_vox_path != 1 &&
-        (ctx->opt_vox_path == 2 || n_points <= (int64_t)32 * ctx->vplan.cells))
+        (ctx->opt_vox_path == 2 || !dense || (int64_t)batch * n_points >= 12000000))
         rc = vox_run_lean(&ctx->vparams, ctx->vplan, ctx->vws, points, counts, batch, n_points, ctx->coors, ctx->num_points,
                           ctx->voxel_count, ctx->offsets, st);
     else

@@ -38,6 +38,7 @@ struct VoxArgs {
     int32_t grid[3];       // nx ny nz
     int32_t cells;
     int32_t K, T, G;
+    int32_t kc_shift;      // set-exact path: chunk of point i = i >> kc_shift (< VL_KC); 0 = counts are not chunked
     int32_t apply_shift;
     float z_shift;
     int32_t max_points, max_voxels, reverse;
@@ -476,7 +477,12 @@ __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxArgs a) {
 // returns: voxel ids in order of first appearance (coors), num_points, and the max_voxels break.  None of that needs the
 // rank of EVERY point inside its cell -- only, for the few over-full cells, the index of their max_points-th point:
 //   vl_count     every point: cell (16 bit) out, RED.ADD on the cell's count, RED.MIN on its first index (one atomic
-//                pair per run of equal cells inside a warp: LiDAR rings stay in a cell for many consecutive points)
+//                pair per run of equal cells inside a warp: LiDAR rings stay in a cell for many consecutive points).
+//                The count is kept per CHUNK of the index range (VL_KC = 8 chunks of 2^kc_shift points): for an
+//                over-full cell the chunk that holds its max_points-th point follows from a prefix over 8 numbers, every
+//                point in an earlier chunk is kept outright, and only the points of THAT chunk are candidates -- an
+//                eighth of the collect / select work on a LiDAR scan, and what makes the path pay on dense camera
+//                frames where every cell is over-full
 //   vl_cells     per cell: voxel id by popcount-prefix over the first-point bitmap, the break index, kept counts and
 //                the two CSR offset arrays (as vox_assign_kernel); over-full cells go on a compact list
 //   vl_collect   points of over-full cells (before the break) -> the cell's candidate list
@@ -497,7 +503,7 @@ __global__ void __launch_bounds__(256) vl_count_kernel(const VoxArgs a) {
     const int64_t base = (int64_t)b * a.N;
     uint16_t *cell16 = a.ws.lrank + base;
     int32_t *first = a.ws.lfirst + (int64_t)b * a.cells;
-    int32_t *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+    int32_t *cnt = a.kc_shift ? a.ws.lcntk + (int64_t)b * a.cells * VL_KC : a.ws.lcnt + (int64_t)b * a.cells;
     const int lane = threadIdx.x & 31;
     if (blockIdx.x == 0 && threadIdx.x < 4) a.ws.lstat[b * 4 + threadIdx.x] = 0;      // consumed by the kernels that follow
     const int nround = (n + 31) & ~31;                                                   // whole warps stay converged
@@ -524,7 +530,8 @@ __global__ void __launch_bounds__(256) vl_count_kernel(const VoxArgs a) {
             if (head && c >= 0) {
                 const unsigned later = heads & ~((2u << lane) - 1u);
                 const int len = (later ? __ffs(later) - 1 : 32) - lane;
-                atomicAdd(cnt + c, len);
+                // (the 32 points of a warp step share a chunk: chunks are multiples of 32 points)
+                atomicAdd(a.kc_shift ? cnt + c * VL_KC + (i >> a.kc_shift) : cnt + c, len);
                 atomicMin(first + c, i);
             }
         }
@@ -743,6 +750,30 @@ __device__ __forceinline__ unsigned long long block_exclusive_scan64(unsigned lo
     return res;
 }
 
+// Chunked counts of one cell (VL_KC consecutive int32): the total, and for an over-full cell the chunk k* that holds its
+// max_points-th point, that point's rank r inside the chunk (1-based) and the chunk's population (the candidates).
+struct ChunkSplit { int total, kstar, r, cand; };
+__device__ __forceinline__ ChunkSplit chunk_split(const int32_t *ck, int max_points) {
+    const int4 lo = __ldcg(reinterpret_cast<const int4 *>(ck)), hi = __ldcg(reinterpret_cast<const int4 *>(ck) + 1);
+    const int v[VL_KC] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    ChunkSplit s;
+    s.total = 0; s.kstar = 0; s.r = max_points; s.cand = 0;
+    bool found = false;
+#pragma unroll
+    for (int k = 0; k < VL_KC; ++k) {
+        if (!found && s.total + v[k] >= max_points) { found = true; s.kstar = k; s.r = max_points - s.total; s.cand = v[k]; }
+        s.total += v[k];
+    }
+    return s;
+}
+// keep-threshold slot of an over-full cell between the per-cell kernel and vl_select: which chunk to collect and the rank
+// to select, as a negative number (-1 = the whole index range, rank max_points: un-chunked counts / after the break)
+__device__ __forceinline__ int thr_encode(int kstar, int r) { return -2 - (kstar | (r << 4)); }
+__device__ __forceinline__ void thr_decode(int t, int max_points, int &kstar, int &r) {
+    if (t >= -1) { kstar = -1; r = max_points; }
+    else { const int code = -2 - t; kstar = code & 15; r = code >> 4; }
+}
+
 __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     extern __shared__ uint32_t s_bm[];             // [nW] first-point bitmap, then (8-byte aligned) [cells] packed counters
     __shared__ int s_tpre[1024];
@@ -757,6 +788,7 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     unsigned long long *s_pk = reinterpret_cast<unsigned long long *>(s_bm + ((nWcap + 2) & ~1));
     int32_t *first = a.ws.lfirst + (int64_t)b * a.cells;
     int32_t *cnt = a.ws.lcnt + (int64_t)b * a.cells;
+    const int32_t *cntk = a.ws.lcntk + (int64_t)b * a.cells * VL_KC;
     int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
     int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
     int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
@@ -768,6 +800,7 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
     int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
     const int cpt = (a.cells + 1023) / 1024;       // <= VL_CPT (checked by the launcher)
+    const bool chunked = a.kc_shift != 0;
 
     // every CTA of the scan looks at ALL cells (first index + count, 2 * cpt coalesced loads in flight): the voxel ids
     // and, when the break does not fire, every offset follow from them without any exchange between the CTAs
@@ -777,7 +810,16 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
         const int c = j * 1024 + tid;
         const bool ok = j < cpt && c < a.cells;
         fa[j] = ok ? __ldcg(first + c) : INT_MAX;
-        ha[j] = ok ? __ldcg(cnt + c) : 0;
+        // ha: the cell's point count, or for an over-full cell MINUS the number of its candidates (chunked counts: the
+        // population of the chunk that holds the max_points-th point; else all of its points)
+        if (!ok) ha[j] = 0;
+        else if (chunked) {
+            const ChunkSplit cs = chunk_split(cntk + (int64_t)c * VL_KC, a.max_points);
+            ha[j] = cs.total > a.max_points ? -cs.cand : cs.total;
+        } else {
+            const int h = __ldcg(cnt + c);
+            ha[j] = h > a.max_points ? -h : h;
+        }
     }
     for (int w = tid; w < nW; w += 1024) s_bm[w] = 0;
     if (tid == 0) s_cut = INT_MAX;
@@ -836,8 +878,8 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
             const int c = j * 1024 + tid;
             if (j < cpt && c < a.cells) {
                 const int h = (fa[j] < n) ? ha[j] : 0;
-                s_pk[c] = (unsigned long long)min(h, a.max_points) |
-                          (h > a.max_points ? (1ull << 21) | ((unsigned long long)h << 36) : 0ull);
+                s_pk[c] = h < 0 ? ((unsigned long long)a.max_points | (1ull << 21) | ((unsigned long long)(-h) << 36))
+                                : (unsigned long long)h;
             }
         }
         __syncthreads();
@@ -857,11 +899,16 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
             const unsigned long long ex = s_pk[c];
             vid[c] = v;
             offc[c] = (int)(ex & 0x1fffffull);
-            if (v >= 0) num[v] = min(h, a.max_points);
-            if (h > a.max_points) {
+            if (v >= 0) num[v] = h < 0 ? a.max_points : h;
+            if (h < 0) {
                 hot[(int)((ex >> 21) & 0x7fffull)] = c;
                 hoff[c] = (int)(ex >> 36);
-                thr[c] = -1;                              // set by vl_select_kernel
+                int code = -1;                            // un-chunked: every point of the cell is a candidate
+                if (chunked) {
+                    const ChunkSplit cs = chunk_split(cntk + (int64_t)c * VL_KC, a.max_points);
+                    code = thr_encode(cs.kstar, cs.r);
+                }
+                thr[c] = code;                            // replaced by the keep threshold in vl_select_kernel
             } else {
                 hoff[c] = -1;
                 thr[c] = (v >= 0) ? INT_MAX : -1;
@@ -953,6 +1000,10 @@ __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
     {   // every CTA of the per-cell kernel has read the first indices / counts by now: restore them for the next call
         int32_t *first = a.ws.lfirst + (int64_t)b * a.cells, *cnt = a.ws.lcnt + (int64_t)b * a.cells;
         for (int c = blockIdx.x * 256 + threadIdx.x; c < a.cells; c += gridDim.x * 256) { first[c] = VL_NONE; cnt[c] = 0; }
+        if (a.kc_shift) {
+            int4 *ck = reinterpret_cast<int4 *>(a.ws.lcntk + (int64_t)b * a.cells * VL_KC);
+            for (int q = blockIdx.x * 256 + threadIdx.x; q < a.cells * (VL_KC / 4); q += gridDim.x * 256) ck[q] = make_int4(0, 0, 0, 0);
+        }
     }
     if (a.ws.lstat[b * 4] == 0) return;                   // no over-full cell in this scan
     const int n = a.counts ? max(0, min(a.counts[b], a.N)) : a.N;
@@ -960,6 +1011,7 @@ __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
     const int64_t base = (int64_t)b * a.N;
     const uint16_t *cell16 = a.ws.lrank + base;
     const int32_t *hoff = a.ws.lhoff + (int64_t)b * a.cells;
+    const int32_t *thr = a.ws.lthr + (int64_t)b * a.cells;
     int32_t *fill = a.ws.lfill + (int64_t)b * a.cells;
     int32_t *cand = a.ws.cell + base;                     // the exact path's cell buffer doubles as the candidate lists
     const int lane = threadIdx.x & 31;
@@ -972,7 +1024,14 @@ __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
 #pragma unroll
         for (int h = 0; h < U; ++h) { i[h] = i0 + h * stride; c[h] = (i[h] < lim) ? (int)cell16[i[h]] : 0xffff; }
 #pragma unroll
-        for (int h = 0; h < U; ++h) o[h] = (c[h] != 0xffff) ? __ldg(hoff + c[h]) : -1;
+        for (int h = 0; h < U; ++h) {
+            o[h] = (c[h] != 0xffff) ? __ldg(hoff + c[h]) : -1;
+            if (o[h] >= 0 && a.kc_shift) {                // chunked counts: only the chunk that holds the max_points-th point
+                int kstar, r;
+                thr_decode(__ldcg(thr + c[h]), a.max_points, kstar, r);
+                if (kstar >= 0 && (i[h] >> a.kc_shift) != kstar) o[h] = -1;
+            }
+        }
 #pragma unroll
         for (int h = 0; h < U; ++h) rs[h] = run_slots_issue(fill + (o[h] >= 0 ? c[h] : 0), c[h], o[h] >= 0, lane);
 #pragma unroll
@@ -998,9 +1057,11 @@ __global__ void __launch_bounds__(VL_SEL_WARPS * 32) vl_select_kernel(const VoxA
     const int32_t *cand_all = a.ws.cell + (int64_t)b * a.N;
     for (int j = blockIdx.x * VL_SEL_WARPS + warp; j < nh; j += gridDim.x * VL_SEL_WARPS) {
         const int c = hot[j];
-        const int m = fill[c];                            // candidates collected (> max_points)
+        const int m = fill[c];                            // candidates collected
         const int32_t *cand = cand_all + hoff[c];
-        if (m <= a.max_points) {                          // cannot happen (the cell would not be on the list); stay safe
+        int kstar, want;                                  // rank (1-based) of the keep threshold among the candidates
+        thr_decode(thr[c], a.max_points, kstar, want);
+        if (m < want) {                                   // cannot happen (the counts say the rank exists); stay safe
             if (lane == 0) { thr[c] = INT_MAX; fill[c] = 0; }
             continue;
         }
@@ -1016,12 +1077,12 @@ __global__ void __launch_bounds__(VL_SEL_WARPS * 32) vl_select_kernel(const VoxA
         for (int k = k0; k < k1; ++k) mine += (int)hist[k];
         const int incl = warp_inclusive_scan(mine);
         const int before_lane = incl - mine;
-        const bool holds = before_lane < a.max_points && a.max_points <= incl;
+        const bool holds = before_lane < want && want <= incl;
         int bstar = 0, before = 0;
         if (holds) {
             int run = before_lane;
             for (int k = k0; k < k1; ++k) {
-                if (run + (int)hist[k] >= a.max_points) { bstar = k; before = run; break; }
+                if (run + (int)hist[k] >= want) { bstar = k; before = run; break; }
                 run += (int)hist[k];
             }
         }
@@ -1034,8 +1095,8 @@ __global__ void __launch_bounds__(VL_SEL_WARPS * 32) vl_select_kernel(const VoxA
             if ((i >> VL_SHIFT) == bstar) atomicOr(&bits[(i >> 5) & 31], 1u << (i & 31));
         }
         __syncwarp();
-        // the r-th set bit (1-based) of the 1024-bit map, r = max_points - before
-        const int r = a.max_points - before;
+        // the r-th set bit (1-based) of the 1024-bit map, r = wanted rank - candidates in earlier buckets
+        const int r = want - before;
         const uint32_t word = bits[lane];
         const int pc = __popc(word);
         const int pincl = warp_inclusive_scan(pc);
@@ -1189,6 +1250,7 @@ size_t vox_carve(const VoxPlan &plan, int32_t batch, int64_t n_points, void *ws,
     const size_t bc = (size_t)batch * plan.cells;
     w.lfirst = lean ? c.take<int32_t>(bc) : nullptr;
     w.lcnt = lean ? c.take<int32_t>(bc) : nullptr;
+    w.lcntk = lean ? c.take<int32_t>(bc * VL_KC) : nullptr;
     w.lfill = lean ? c.take<int32_t>(bc) : nullptr;
     w.lthr = lean ? c.take<int32_t>(bc) : nullptr;
     w.lhoff = lean ? c.take<int32_t>(bc) : nullptr;
@@ -1209,6 +1271,7 @@ static void fill_args(VoxArgs &a, const gnd_voxel_params *p, const VoxPlan &plan
         a.inv[j] = (m == 0.5f && e > -100 && e < 100) ? 1.0f / a.vs[j] : 0.0f;
     }
     a.cells = plan.cells; a.K = plan.K; a.T = plan.T; a.G = plan.G;
+    a.kc_shift = 0;
     a.apply_shift = p->apply_z_shift; a.z_shift = p->z_shift;
     a.max_points = p->max_points; a.max_voxels = p->max_voxels; a.reverse = p->reverse_index;
     a.ws = ws;
@@ -1232,6 +1295,7 @@ int vox_lean_init(const VoxPlan &plan, const VoxWs &ws, int32_t batch) {      //
     const size_t bc = (size_t)batch * plan.cells;
     GND_CUDA_CHECK(cudaMemset(ws.lfirst, 0x7f, bc * sizeof(int32_t)));
     GND_CUDA_CHECK(cudaMemset(ws.lcnt, 0, bc * sizeof(int32_t)));
+    GND_CUDA_CHECK(cudaMemset(ws.lcntk, 0, bc * VL_KC * sizeof(int32_t)));
     GND_CUDA_CHECK(cudaMemset(ws.lfill, 0, bc * sizeof(int32_t)));
     GND_CUDA_CHECK(cudaMemset(ws.lstat, 0, (size_t)batch * 4 * sizeof(int32_t)));
     return GND_OK;
@@ -1250,6 +1314,18 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
     a.list = nullptr; a.voxels = nullptr; a.slot = nullptr;
     int rc = vl_attrs();
     if (rc != GND_OK) return rc;
+    const int64_t n_cap = n_points;
+    const size_t smem1 = (size_t)(((n_cap + 31) / 32 + 2) & ~(size_t)1) * sizeof(uint32_t) + (size_t)plan.cells * sizeof(unsigned long long) + 16;
+    const bool single = plan.cells <= 1024 * VL_CPT && smem1 <= 200 * 1024;
+    // chunked counts pay on DENSE clouds only (camera frames: every cell over-full, ~400 points each): measured at
+    // 64 x 1 M points 1.61 ms against 2.03 ms for the order-exact kernels (un-chunked set-exact: slower than both), but
+    // on LiDAR scans +0.02 ms per 64 scans (8 counters per cell to read and to clear, one more dependent gather per
+    // candidate) against the 0.01 ms the smaller candidate lists save
+    if (single && n_points > (int64_t)32 * plan.cells) {     // VL_KC chunks of 2^kc_shift points
+        int sh = 5;
+        while (((int64_t)VL_KC << sh) < n_points) ++sh;
+        a.kc_shift = sh;
+    }
     // point-parallel kernels: about eight CTAs per SM over the whole batch
     int gx = (int)((n_points + 255) / 256);
     const int want = (148 * 8 + batch - 1) / batch;
@@ -1257,9 +1333,7 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
     if (gx < 1) gx = 1;
     vl_count_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
     GND_LAUNCH_CHECK("vl_count_kernel");
-    const int64_t n_cap = n_points;
-    const size_t smem1 = (size_t)(((n_cap + 31) / 32 + 2) & ~(size_t)1) * sizeof(uint32_t) + (size_t)plan.cells * sizeof(unsigned long long) + 16;
-    if (plan.cells <= 1024 * VL_CPT && smem1 <= 200 * 1024) {
+    if (single) {
         // every CTA of a scan redoes the all-cells part: as few CTAs per scan as still fill the SMs
         int g = 148 / batch;
         a.G = g < 1 ? 1 : (g > 16 ? 16 : g);

@@ -12,6 +12,7 @@ constexpr int VOX_RT_WARPS = 8;
 constexpr int VOX_RT_STEPS = 7;
 constexpr int VOX_RT_TILE = VOX_RT_WARPS * VOX_RT_STEPS * 32;
 constexpr int VOX_RT_MAX_CELLS = 11264;   // 10 bytes of shared memory per cell, two CTAs per SM
+constexpr int VL_KC = 8;             // set-exact path: chunks of the index range that the per-cell counts are kept for
 
 struct VoxPlan {
     int32_t grid[3];     // nx, ny, nz   (utils/point_cloud_ops.py:24-27)
@@ -39,6 +40,7 @@ struct VoxWs {
     // ---- set-exact ("lean") path of the fused pipeline: private, self-resetting state (see voxelize.cu) ----
     int32_t *lfirst;     // [B][cells]  index of the cell's first in-range point (INT_MAX-like between calls)
     int32_t *lcnt;       // [B][cells]  in-range points of the cell (0 between calls)
+    int32_t *lcntk;      // [B][cells][VL_KC] the same count per CHUNK of the index range (single-CTA per-cell kernel only)
     int32_t *lfill;      // [B][cells]  slot counter / collected-candidate counter
     int32_t *lthr;       // [B][cells]  largest kept point index of the cell (INT_MAX: keep all)
     int32_t *lhoff;      // [B][cells]  offset of the cell's candidate list in hot_idx, -1 if the cell is not over-full

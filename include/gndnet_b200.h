@@ -296,8 +296,9 @@ GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
  *                    CUDA-core kernel runs)
  *   "vox_path"       gnd_infer only: 0 = automatic (default): set-exact voxelization -- same coors / num_points /
  *                    voxel_count and the same kept points per pillar, but no slot-ordered point_list / offsets -- unless
- *                    the cloud is dense (more than 32 points per cell on average), 1 = always the order-exact kernels
- *                    gnd_voxelize uses (point_list filled), 2 = always the set-exact kernels */
+ *                    the cloud is dense (more than 32 points per cell on average) and the batch small (< 12 M points
+ *                    in all), 1 = always the order-exact kernels gnd_voxelize uses (point_list filled), 2 = always
+ *                    the set-exact kernels */
 GND_API int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value);
 /* Asynchronous per-convolution timing for bench.py's roofline: after _begin, each of the next `slots` gnd_segnet /
  * gnd_infer calls records library-owned CUDA events around its 8 convolution launches (nothing is read back, the

@@ -225,3 +225,50 @@ def test_fused_set_exact_voxelizer_on_a_large_grid(cuda):
             assert torch.equal(pl["cell_offsets"], pe["cell_offsets"])
             assert torch.equal(hl, he) and torch.equal(ll, le)
         model.release()
+
+
+@pytest.mark.parametrize("max_voxels", [2500, 700])
+def test_fused_set_exact_voxelizer_dense_cloud_chunked_counts(max_voxels, cuda):
+    """Dense clouds (> 32 points per cell: the camera frames) keep the per-cell counts per CHUNK of the index range, so
+    that only the chunk holding a cell's max_points-th point is searched.  Two different 300 k-point frames in one
+    batch (every cell over-full, max_points truncation everywhere), with and without the max_voxels break: coors /
+    num_points against the oracle, kept sets / heights / labels against the order-exact kernels, twice (self-resetting
+    state)."""
+    from tests import helpers
+    cfg = synth.make_cfg("camera", max_voxels=max_voxels, batch_size=2)
+    model, sd = helpers.load_model(cfg, "camera", "mixed", cuda)
+    raws = [synth.camera_scan(31)[:300000].copy(), synth.camera_scan(32)[100000:400000].copy()]
+    pts = torch.from_numpy(np.stack(raws)).cuda().contiguous()
+    assert pts.shape[1] > 32 * 2500
+    res = {}
+    with torch.no_grad():
+        for path in (1, 2, 2):
+            model.set_option("vox_path", path)
+            h, l = model.infer(pts, threshold=0.08, labels="int8")
+            pil = {k: v.clone() for k, v in model.pillars(2).items()}
+            res.setdefault(path, []).append((h.clone(), l.clone(), pil))
+    (he, le, pe), = res[1]
+    for b, raw in enumerate(raws):
+        p = _shifted(cfg, raw)
+        ov, oc, on = cpu_ops.points_to_voxel(p, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+        m = len(on)
+        assert m == min(max_voxels, 2500) or m < max_voxels
+        for hl, ll, pl in res[2] + res[1]:
+            assert int(pl["voxel_count"][b]) == m
+            assert np.array_equal(pl["coors"][b, :m].cpu().numpy(), oc) and np.array_equal(pl["num_points"][b, :m].cpu().numpy(), on)
+    for hl, ll, pl in res[2]:
+        assert torch.equal(pl["cell_offsets"], pe["cell_offsets"])
+        for b in range(2):
+            kept = int(pe["cell_offsets"][b, -1])
+            offs = pe["cell_offsets"][b].long()
+            seg = torch.repeat_interleave(torch.arange(offs.numel() - 1, device="cuda"), offs[1:] - offs[:-1])
+
+            def canon(rows):
+                rows = rows[:kept]
+                order = torch.arange(kept, device="cuda")
+                for col in (3, 2, 1, 0):
+                    order = order[torch.argsort(rows[order, col], stable=True)]
+                return rows[order[torch.argsort(seg[order], stable=True)]]
+            assert torch.equal(canon(pl["cell_points"][b]), canon(pe["cell_points"][b])), "kept point sets differ"
+        assert torch.equal(hl, he) and torch.equal(ll, le)
+    model.release()
