@@ -63,11 +63,12 @@ size_t carve_all(gnd_ctx *ctx, int B, int64_t N, void *ws, std::vector<NamedBuf>
     uint8_t *idx1 = c.take<uint8_t>((size_t)B * H1 * W1 * 128);
     float *regpart = (prec == GND_PREC_FP32) ? nullptr : c.take<float>((size_t)B * H * W * 9);
     int32_t *pfn_ctr = c.take<int32_t>(4);
+    int32_t *pfn_order = c.take<int32_t>((size_t)6 * ctx->nx * ctx->ny * ctx->nz);
     double *bn_partial = cfg.bn_batch_stats ? c.take<double>((size_t)BN_BLOCKS * 256 * 2) : nullptr;
     float *bn_ab = cfg.bn_batch_stats ? c.take<float>(512) : nullptr;
     float *bn_stats = cfg.bn_batch_stats ? c.take<float>(8 * 512) : nullptr;
     if (ws) {
-        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr; ctx->bn_partial = bn_partial; ctx->bn_ab = bn_ab; ctx->bn_stats = bn_stats;
+        ctx->idx1 = idx1; ctx->regpart = regpart; ctx->pfn_ctr = pfn_ctr; ctx->pfn_order = pfn_order; ctx->bn_partial = bn_partial; ctx->bn_ab = bn_ab; ctx->bn_stats = bn_stats;
         if (names) {
             names->push_back({"idx1", idx1, (size_t)B * H1 * W1 * 128});
             if (regpart) names->push_back({"regpart", regpart, (size_t)B * H * W * 9 * 4});
@@ -132,6 +133,8 @@ extern "C" int gnd_bind_workspace(gnd_ctx *ctx, void *workspace, size_t bytes, i
     ctx->ws = workspace; ctx->ws_bytes = bytes; ctx->B = batch; ctx->N = n_points;
     carve_all(ctx, batch, n_points, workspace, nullptr);
     GND_CUDA_CHECK(cudaMemset(ctx->pfn_ctr, 0, 4 * sizeof(int32_t)));
+    rc = pfn_build_order(ctx);
+    if (rc != GND_OK) { ctx->ws = nullptr; return rc; }
     rc = vox_lean_init(ctx->vplan, ctx->vws, batch);
     if (rc != GND_OK) { ctx->ws = nullptr; return rc; }
     if (ctx->cfg.precision != GND_PREC_FP32 && ctx->weights_loaded) {

@@ -72,6 +72,7 @@ struct gnd_ctx {
     float *bn_ab = nullptr;         // [2][256] per-channel scale / shift of the current layer
     float *bn_stats = nullptr;      // [8][256][2] batch mean / unbiased variance of every conv block (bn_batch_stats)
     int32_t *pfn_ctr = nullptr; // [2] work-queue head + finished-CTA count of pfn_scatter_kernel (self-resetting)
+    int32_t *pfn_order = nullptr;   // [6][cells] work units of 2^s cells (s = 0..5) sorted by distance from the sensor's cell
     gnd::TensorMaps *tmaps = nullptr;
     gnd::Halo2Maps *h2maps = nullptr;
 
@@ -93,6 +94,7 @@ struct gnd_ctx {
 namespace gnd {
 
 // pfn.cu
+int pfn_build_order(gnd_ctx *ctx);          // set-up time: distance-sorted work-unit lists into ctx->pfn_order
 int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_points, cudaStream_t st);
 int pfn_scatter_dense_run(gnd_ctx *ctx, const float *voxels, const float *coors4, const float *num_points,
                           int64_t n_pillars, int32_t batch, cudaStream_t st);

@@ -774,6 +774,7 @@ __device__ __forceinline__ void thr_decode(int t, int max_points, int &kstar, in
     else { const int code = -2 - t; kstar = code & 15; r = code >> 4; }
 }
 
+template <bool CHUNKED>
 __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     extern __shared__ uint32_t s_bm[];             // [nW] first-point bitmap, then (8-byte aligned) [cells] packed counters
     __shared__ int s_tpre[1024];
@@ -800,7 +801,7 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     int32_t *off = a.offsets + (int64_t)b * (a.max_voxels + 1);
     int32_t *offc = a.ws.offc + (int64_t)b * (a.cells + 1);
     const int cpt = (a.cells + 1023) / 1024;       // <= VL_CPT (checked by the launcher)
-    const bool chunked = a.kc_shift != 0;
+    constexpr bool chunked = CHUNKED;         // compile-time: the un-chunked instance keeps its 2 * cpt plain loads in flight
 
     // every CTA of the scan looks at ALL cells (first index + count, 2 * cpt coalesced loads in flight): the voxel ids
     // and, when the break does not fire, every offset follow from them without any exchange between the CTAs
@@ -995,12 +996,13 @@ __global__ void __launch_bounds__(1024) vl_cells1_kernel(const VoxArgs a) {
     }
 }
 
+template <bool CHUNKED>
 __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
     const int b = blockIdx.y;
     {   // every CTA of the per-cell kernel has read the first indices / counts by now: restore them for the next call
         int32_t *first = a.ws.lfirst + (int64_t)b * a.cells, *cnt = a.ws.lcnt + (int64_t)b * a.cells;
         for (int c = blockIdx.x * 256 + threadIdx.x; c < a.cells; c += gridDim.x * 256) { first[c] = VL_NONE; cnt[c] = 0; }
-        if (a.kc_shift) {
+        if (CHUNKED) {
             int4 *ck = reinterpret_cast<int4 *>(a.ws.lcntk + (int64_t)b * a.cells * VL_KC);
             for (int q = blockIdx.x * 256 + threadIdx.x; q < a.cells * (VL_KC / 4); q += gridDim.x * 256) ck[q] = make_int4(0, 0, 0, 0);
         }
@@ -1026,7 +1028,7 @@ __global__ void __launch_bounds__(256) vl_collect_kernel(const VoxArgs a) {
 #pragma unroll
         for (int h = 0; h < U; ++h) {
             o[h] = (c[h] != 0xffff) ? __ldg(hoff + c[h]) : -1;
-            if (o[h] >= 0 && a.kc_shift) {                // chunked counts: only the chunk that holds the max_points-th point
+            if (CHUNKED && o[h] >= 0) {                   // chunked counts: only the chunk that holds the max_points-th point
                 int kstar, r;
                 thr_decode(__ldcg(thr + c[h]), a.max_points, kstar, r);
                 if (kstar >= 0 && (i[h] >> a.kc_shift) != kstar) o[h] = -1;
@@ -1283,7 +1285,8 @@ static int vl_attrs() {
     GND_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !done[dev]) {
         GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
-        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells1_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
+        GND_CUDA_CHECK(cudaFuncSetAttribute(vl_cells1_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 8));
         GND_CUDA_CHECK(cudaFuncSetAttribute(vl_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         if (dev >= 0 && dev < 64) done[dev] = true;
     }
@@ -1337,14 +1340,16 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
         // every CTA of a scan redoes the all-cells part: as few CTAs per scan as still fill the SMs
         int g = 148 / batch;
         a.G = g < 1 ? 1 : (g > 16 ? 16 : g);
-        vl_cells1_kernel<<<batch * a.G, 1024, smem1, stream>>>(a);
+        if (a.kc_shift) vl_cells1_kernel<true><<<batch * a.G, 1024, smem1, stream>>>(a);
+        else vl_cells1_kernel<false><<<batch * a.G, 1024, smem1, stream>>>(a);
         GND_LAUNCH_CHECK("vl_cells1_kernel");
     } else {
         vl_cells_kernel<<<batch * plan.G, 1024, plan.assign_smem, stream>>>(a);
         GND_LAUNCH_CHECK("vl_cells_kernel");
     }
     if (n_points > 0) {
-        vl_collect_kernel<<<dim3(gx, batch), 256, 0, stream>>>(a);
+        if (a.kc_shift) vl_collect_kernel<true><<<dim3(gx, batch), 256, 0, stream>>>(a);
+        else vl_collect_kernel<false><<<dim3(gx, batch), 256, 0, stream>>>(a);
         GND_LAUNCH_CHECK("vl_collect_kernel");
         const int nbuckets = (int)(n_points >> VL_SHIFT) + 1;
         int sx = (148 * 4 + batch - 1) / batch;
