@@ -164,6 +164,10 @@ __device__ __forceinline__ void zero_empty_cells(const PfnArgs &a, int64_t cell0
 template <bool DIST, bool HAS_R>
 __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const PfnArgs a) {
     __shared__ float4 s_pt[PFN_WARPS][32];
+    // without the |p| feature the points are staged in PAIRS, (x'a, x'b, y'a, y'b) (za, zb, ra, rb): two LDS.128 deliver, for
+    // two points at once, the aligned register pairs of sm_100's packed fma.rn.f32x2 -- per point and channel pair 4 packed
+    // FMAs + 1 FMNMX3 + 1 LDS instead of 8 FFMA + 2 FMNMX + 1 LDS, same arithmetic per point
+    __shared__ float4 s_pp[PFN_WARPS][16][2];
     __shared__ float s_dist[PFN_WARPS][32];
     __shared__ float2 s_rq[PFN_RQ];                // (1/n) * iq_xy, (1/n) * iq_z: one LDS instead of an IEEE reciprocal per cell
     for (int i = threadIdx.x; i < PFN_RQ; i += PFN_WARPS * 32) {
@@ -185,6 +189,8 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
     const float G0 = DIST ? W(kf + 5, ch0) : 0.0f, G1 = DIST ? W(kf + 5, ch1) : 0.0f;
     const float b0 = __ldg(a.bias + ch0), b1 = __ldg(a.bias + ch1);
     const float rb0 = fmaxf(b0, 0.0f), rb1 = fmaxf(b1, 0.0f);
+    float *const pr = reinterpret_cast<float *>(&s_pp[warp][lane >> 1][0]) + (lane & 1);      // this lane's slot of its pair
+    const float4 *const pp = &s_pp[warp][0][0];
     const int cells = a.nx * a.ny;
     const int gsize = 1 << a.gshift;
     const int groups = (cells + gsize - 1) >> a.gshift;
@@ -250,7 +256,11 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
                         float4 f = f0;
                         float4 p = p0;
                         if (q0 != 0) { p = __ldg(pts + o + q0 + lane); f = make_float4(p.x - pcx, p.y - pcy, p.z, p.w); }
-                        s_pt[warp][lane] = f;
+                        if (DIST) s_pt[warp][lane] = f;
+                        else {
+                            pr[0] = f.x; pr[2] = f.y; pr[4] = f.z; pr[6] = f.w;
+                            if (q0 + lane == n - 1 && !(lane & 1)) { pr[1] = f.x; pr[3] = f.y; pr[5] = f.z; pr[7] = f.w; }   // odd count: the last point twice
+                        }
                         if (DIST) s_dist[warp][lane] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(p.x, p.x), __fmul_rn(p.y, p.y)), __fmul_rn(p.z, p.z)));
                     }
                     __syncwarp();
@@ -263,18 +273,19 @@ __global__ void __launch_bounds__(PFN_WARPS * 32, 4) pfn_scatter_kernel(const Pf
                             t1 = fmaxf(t1, fmaf(G1, dq, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x)))));
                         }
                     } else {
-                        // (pairing two points per step so that the maximum is one FMNMX3 per channel was measured: 0.215 ms
-                        //  against 0.207 ms for this form)
-#pragma unroll 4
-                        for (int q = 0; q < cnt; ++q) {
-                            const float4 f = s_pt[warp][q];
-                            if (HAS_R) {
-                                t0 = fmaxf(t0, fmaf(D0, f.w, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x))));
-                                t1 = fmaxf(t1, fmaf(D1, f.w, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x))));
-                            } else {
-                                t0 = fmaxf(t0, fmaf(C0, f.z, fmaf(B0, f.y, A0 * f.x)));
-                                t1 = fmaxf(t1, fmaf(C1, f.z, fmaf(B1, f.y, A1 * f.x)));
-                            }
+                        const float2 A00 = make_float2(A0, A0), A11 = make_float2(A1, A1), B00 = make_float2(B0, B0), B11 = make_float2(B1, B1);
+                        const float2 C00 = make_float2(C0, C0), C11 = make_float2(C1, C1), D00 = make_float2(D0, D0), D11 = make_float2(D1, D1);
+                        const int npair = (cnt + 1) >> 1;
+#pragma unroll 2
+                        for (int q = 0; q < npair; ++q) {
+                            const float4 fa = pp[2 * q], fb = pp[2 * q + 1];
+                            const float2 xx = make_float2(fa.x, fa.y), yy = make_float2(fa.z, fa.w), zz = make_float2(fb.x, fb.y), rr = make_float2(fb.z, fb.w);
+                            // per point and channel the same order as the scalar form: mul, then two (three) fused multiply-adds
+                            float2 u = __ffma2_rn(C00, zz, __ffma2_rn(B00, yy, __fmul2_rn(A00, xx)));
+                            float2 v = __ffma2_rn(C11, zz, __ffma2_rn(B11, yy, __fmul2_rn(A11, xx)));
+                            if (HAS_R) { u = __ffma2_rn(D00, rr, u); v = __ffma2_rn(D11, rr, v); }
+                            t0 = fmaxf(t0, fmaxf(u.x, u.y));
+                            t1 = fmaxf(t1, fmaxf(v.x, v.y));
                         }
                     }
                     __syncwarp();
