@@ -414,6 +414,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="only value / e2e (profiling runs)")
     ap.add_argument("--soak", type=float, default=0.6, help="seconds of un-timed soak before each timed region")
+    ap.add_argument("--no-graph", action="store_true", help="resident steps and ScanStream as direct launches instead of CUDA-graph replays")
     ap.add_argument("--split", type=int, default=1, help="e2e: sub-batches per submitted batch (default 1: measured best at N = 1 and 2 -- 26.4k / 24.7k / 21.4k / 15.5k scans/s for 1 / 2 / 4 / 8 on one GPU: the extra enqueues cost more than the shorter ramp saves)")
     ap.add_argument("--equal-shards", action="store_true", help="e2e: equal shards instead of link-rate-proportional ones")
     ap.add_argument("--ref-scans-per-step", type=int, default=8, help="--impl reference: scans timed per step (bounded sample of the batch)")
@@ -483,10 +484,26 @@ def main():
     rates = gather_rates(my_rate, device=dev)
     shards = [B] * world if (world == 1 or args.equal_shards) else rate_shards(rates, world * B, max(8, B // 2), Bmax)
     my_b = shards[rank]
-    pipe = ScanStream(model, Bmax, N_POINTS, depth=2, labels="int8", threshold=0.08, split=max(1, args.split))
+    pipe = ScanStream(model, Bmax, N_POINTS, depth=2, labels="int8", threshold=0.08, split=max(1, args.split), use_graph=not args.no_graph)
+
+    def step_direct(i):
+        model.infer(resident[i & 1], threshold=0.08, out=(height, labels))
+
+    # the resident step through the public API's graph front end (gndnet_b200.pipeline.GraphedInfer): the 19 launches of a
+    # 64-scan step captured once per resident batch, one replay per step (ScanStream does the same for host-fed batches)
+    gres = None
+    if not args.no_graph:
+        with torch.no_grad():
+            gres = [GraphedInfer(model, B, N_POINTS, threshold=0.08, labels="int8") for _ in range(2)]
+            for k in range(2):
+                gres[k].points.copy_(resident[k])
+        torch.cuda.synchronize()
 
     def step_resident(i):
-        model.infer(resident[i & 1], threshold=0.08, out=(height, labels))
+        if gres is not None:
+            gres[i & 1]()
+        else:
+            step_direct(i)
 
     def step_e2e(i):
         # host buffers in, host buffers out: pinned H2D of this step's scans and D2H of its height maps + labels,
@@ -581,11 +598,11 @@ def main():
         pk = peaks()
         with torch.no_grad():
             # ---- roofline: the 8 conv launches timed INSIDE a long back-to-back run (sustained clocks)
-            soak(step_resident, max(args.soak, 0.5))
+            soak(step_direct, max(args.soak, 0.5))
             n_t = 96
             model.conv_timing_begin(n_t)
             for i in range(n_t):
-                step_resident(i)
+                step_direct(i)
             conv_ms_all, seg_ms_all, stage_ms_all = model.conv_timing_end(stages=True)
         conv_layers = conv_ms_all.mean(axis=0)
         conv_ms = float(conv_layers.sum())
@@ -664,7 +681,19 @@ def main():
         with torch.no_grad():
             model.infer(resident[0], threshold=0.08, out=(height, labels))
             torch.cuda.synchronize()
-            soak(step_resident, 0.3)
+            # the same resident step as 19 direct launches per step (what the graph replay saves at batch 64)
+            soak(step_direct, 0.5)
+            ga, gb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ga.record()
+            for i in range(args.steps):
+                step_direct(i)
+            gb.record()
+            torch.cuda.synchronize()
+            ms_d = ga.elapsed_time(gb) / args.steps
+            extra["value_direct_launches"] = {"value": B / ms_d * 1e3, "unit": "scans/s", "ms_per_step": ms_d,
+                                              "note": "inputs resident; model.infer() called per step (19 kernel launches) instead of "
+                                                      "one CUDA-graph replay" if gres is not None else "same as value (--no-graph)"}
+            soak(step_direct, 0.3)
             st = model.stage_times(resident[1], height, labels, reps=5)
         extra["stage_ms_stage_calls"] = st
         extra["stage_ms_stage_calls_note"] = ("the four stage entry points of the C ABI (gnd_voxelize = the ORDER-exact voxelizer that "
@@ -726,7 +755,9 @@ def main():
                 "config": {"workload": "GndNet kittiSem inference, synthetic 120k-point HDL-64 scans, streaming batch %d per GPU" % B,
                            "points_per_scan": N_POINTS, "batch_per_gpu": B, "global_batch": B * world, "precision": args.precision,
                            "checkpoint": ck, "l2": "inputs larger than L2: two distinct %d MB batches rotated every step" % (B * N_POINTS * 16 // 1000000),
-                           "parallelism": "scans sharded by rank, no collective"},
+                           "parallelism": "scans sharded by rank, no collective",
+                           "launch": ("one CUDA-graph replay per step (19 kernels each; GraphedInfer / ScanStream)" if gres is not None
+                                      else "19 direct kernel launches per step")},
                 "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": int(sum(shards) * SCAN_BYTES // world),
                         "d2h_bytes_per_step": int(sum(shards) * (model.ny * model.nx * 4 + N_POINTS) // world),
                         "bytes_note": "per rank, average over ranks", "ms_per_step": ms_e2e / args.steps, "soak_s": soak_e,

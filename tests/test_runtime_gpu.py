@@ -226,3 +226,40 @@ def test_infer_argument_validation(cuda):
         h, l = model.infer(pts, counts=torch.tensor([-5, n + 1000], dtype=torch.int32).cuda(), labels="int8")
         assert torch.equal(h, h_ref) and torch.equal(l, l_ref)
         assert bool((l[0] == -1).all())
+
+
+def test_scan_stream_host_buffers_match_direct_infer_with_and_without_graphs(cuda):
+    """gndnet_b200.pipeline.ScanStream (pinned host scans in, host results out, three streams): every submitted batch
+    gives byte for byte what infer() gives on the same scans -- with direct launches, and with the CUDA-graph replay
+    that takes over the third time a (slot, row range) is submitted; shorter batches and changed weights in between."""
+    from gndnet_b200.pipeline import ScanStream
+    cfg = synth.make_cfg("kitti", batch_size=1)
+    model, sd = helpers.load_model(cfg, "kitti", "mixed", cuda)
+    N = 20000
+    scans = [synth.hdl64_scan(40 + i)[::6][:N].copy() for i in range(6)]
+    batches = [torch.from_numpy(np.stack(scans[i:i + 3])).pin_memory() for i in (0, 3)]
+    expect = []
+    with torch.no_grad():
+        for hb in batches:
+            h, l = model.infer(hb.cuda(), threshold=0.08, labels="int8")
+            expect.append((h.cpu().clone(), l.cpu().clone()))
+    for use_graph in (False, True):
+        pipe = ScanStream(model, 3, N, depth=2, use_graph=use_graph)
+        with torch.no_grad():
+            for it in range(8):                         # each slot / range is seen four times: direct, capture, replay, replay
+                k = pipe.submit(batches[it & 1])
+                h, l = pipe.result(k)
+                assert torch.equal(h, expect[it & 1][0]) and torch.equal(l, expect[it & 1][1]), (use_graph, it)
+            k = pipe.submit(batches[1][:2])             # a shorter batch through the same slots
+            h, l = pipe.result(k)
+            assert torch.equal(h, expect[1][0][:2]) and torch.equal(l, expect[1][1][:2])
+        if use_graph:
+            assert any(not isinstance(g, str) for g in pipe._graphs.values()), "no graph was captured"
+            # new weights: the captured graphs are dropped, results follow the new weights
+            with torch.no_grad():
+                model.encoder_decoder.regressor.bias.add_(0.25)
+                k = pipe.submit(batches[0])
+                h, l = pipe.result(k)
+                assert torch.allclose(h, expect[0][0] + 0.25, atol=1e-6)
+                model.encoder_decoder.regressor.bias.sub_(0.25)
+    model.release()
