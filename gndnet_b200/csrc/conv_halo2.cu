@@ -207,7 +207,7 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
     uint64_t *bars = reinterpret_cast<uint64_t *>(ring_b + (size_t)p.SB * p.b_stage);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + H2_NBARS);
     float *s_bias = reinterpret_cast<float *>(tmem_slot + 4);           // [256]
-    float *s_regw = s_bias + 256;                                        // [64][12] (fused regressor only)
+    float *s_regw = s_bias + 256;                                        // [32 channel pairs][20] (fused regressor only)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_rank();
     const bool leader = rank == 0;
@@ -238,8 +238,12 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
     if (threadIdx.x >= 128) {
         for (int i = threadIdx.x - 128; i < p.Cout && i < 256; i += 128) s_bias[i] = p.bias[i];
         if (p.regpart)
-            for (int i = threadIdx.x - 128; i < 640; i += 128)       // [tap][c] -> [c][tap]; slot 9 of a row = the conv bias of c
-                s_regw[(i & 63) * 12 + (i >> 6)] = (i < 576) ? p.reg_w[i] : p.bias[i - 576];
+            // [tap][c] -> per channel PAIR (c, c + 1): nine (w[tap][c], w[tap][c + 1]) pairs, then the pair of conv biases:
+            // five 16-byte rows whose halves are the register pairs of the packed fma.rn.f32x2 below
+            for (int i = threadIdx.x - 128; i < 640; i += 128) {
+                const int c = (i < 576) ? (i & 63) : i - 576, slot = (i < 576) ? (i >> 6) : 9;
+                s_regw[(c >> 1) * 20 + slot * 2 + (c & 1)] = (i < 576) ? p.reg_w[i] : p.bias[c];
+            }
     }
     tc_fence_before();
     __syncthreads();
@@ -348,32 +352,32 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
                 const size_t pix = ((size_t)it.b * p.H + y) * p.W + x;
                 const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(acc * 256 + t * p.NT);
                 if (p.regpart) {
-                    float part[9];
+                    // two channels per step through the packed FP32 pipe: 9 FFMA2 + 1 FADD2 + 2 FMNMX + 5 LDS.128 per channel PAIR
+                    // (was 18 FFMA + 2 FADD + 2 FMNMX + 6 LDS.128); even and odd channels accumulate apart and meet at the end
+                    float2 acc[9];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) part[k] = 0.0f;
+                    for (int k = 0; k < 9; ++k) acc[k] = make_float2(0.0f, 0.0f);
 #pragma unroll 1
                     for (int j = 0; j < 2; ++j) {
                         uint32_t v[32];
                         tc_ld_32x32(taddr + 32 * j, v);
                         tc_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const int c = 32 * j + i;
-                            const float4 w0 = *reinterpret_cast<const float4 *>(s_regw + c * 12);
-                            const float4 w1 = *reinterpret_cast<const float4 *>(s_regw + c * 12 + 4);
-                            const float4 w2 = *reinterpret_cast<const float4 *>(s_regw + c * 12 + 8);     // (tap 8, bias, -, -)
-                            const float xv = fmaxf(__uint_as_float(v[i]) + w2.y, 0.0f);
-                            const float w8 = w2.x;
-                            part[0] = fmaf(xv, w0.x, part[0]); part[1] = fmaf(xv, w0.y, part[1]);
-                            part[2] = fmaf(xv, w0.z, part[2]); part[3] = fmaf(xv, w0.w, part[3]);
-                            part[4] = fmaf(xv, w1.x, part[4]); part[5] = fmaf(xv, w1.y, part[5]);
-                            part[6] = fmaf(xv, w1.z, part[6]); part[7] = fmaf(xv, w1.w, part[7]);
-                            part[8] = fmaf(xv, w8, part[8]);
+                        for (int i = 0; i < 16; ++i) {
+                            const float4 *w = reinterpret_cast<const float4 *>(s_regw + (16 * j + i) * 20);
+                            const float4 q0 = w[0], q1 = w[1], q2 = w[2], q3 = w[3], q4 = w[4];       // q4 = (tap 8 pair, bias pair)
+                            float2 x = __fadd2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), make_float2(q4.z, q4.w));
+                            x.x = fmaxf(x.x, 0.0f); x.y = fmaxf(x.y, 0.0f);
+                            acc[0] = __ffma2_rn(x, make_float2(q0.x, q0.y), acc[0]); acc[1] = __ffma2_rn(x, make_float2(q0.z, q0.w), acc[1]);
+                            acc[2] = __ffma2_rn(x, make_float2(q1.x, q1.y), acc[2]); acc[3] = __ffma2_rn(x, make_float2(q1.z, q1.w), acc[3]);
+                            acc[4] = __ffma2_rn(x, make_float2(q2.x, q2.y), acc[4]); acc[5] = __ffma2_rn(x, make_float2(q2.z, q2.w), acc[5]);
+                            acc[6] = __ffma2_rn(x, make_float2(q3.x, q3.y), acc[6]); acc[7] = __ffma2_rn(x, make_float2(q3.z, q3.w), acc[7]);
+                            acc[8] = __ffma2_rn(x, make_float2(q4.x, q4.y), acc[8]);
                         }
                     }
                     if (valid) {
 #pragma unroll
-                        for (int k = 0; k < 9; ++k) p.regpart[pix * 9 + k] = part[k];
+                        for (int k = 0; k < 9; ++k) p.regpart[pix * 9 + k] = acc[k].x + acc[k].y;
                     }
                 } else {
 #pragma unroll 1
