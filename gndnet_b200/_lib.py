@@ -39,7 +39,8 @@ class Config(ctypes.Structure):
     _fields_ = [("pc_range", c_f * 6), ("voxel_size", c_f * 3), ("pc_range_f64", c_d * 6),
                 ("voxel_size_f64", c_d * 3), ("grid_range", c_d * 4), ("lidar_height", c_f),
                 ("max_points_voxel", c_i32), ("max_voxels", c_i32), ("input_features", c_i32),
-                ("use_norm", c_i32), ("with_distance", c_i32), ("precision", c_i32), ("bn_batch_stats", c_i32)]
+                ("use_norm", c_i32), ("with_distance", c_i32), ("precision", c_i32), ("bn_batch_stats", c_i32),
+                ("n_vfe", c_i32), ("vfe_filters", c_i32 * 4)]
 
 
 class UnpackParams(ctypes.Structure):

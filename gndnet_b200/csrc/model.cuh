@@ -50,8 +50,14 @@ struct gnd_ctx {
 
     // weights (device)
     bool weights_loaded = false;
-    float *pfn_w = nullptr;    // [nfeat][64], BatchNorm1d folded when use_norm
+    float *pfn_w = nullptr;    // [nfeat][64], BatchNorm1d folded when use_norm (= vfe_w[0] when there is one PFN layer)
     float *pfn_b = nullptr;    // [64]
+    // multi-layer PillarFeatureNet (cfg.vfe_filters with more than one entry; no shipped config): layer l maps vfe_in[l]
+    // inputs to vfe_units[l] units (out / 2 for the non-last layers, whose output is concat(x, max over the pillar))
+    int n_vfe = 1;
+    int vfe_in[4] = {0, 0, 0, 0}, vfe_units[4] = {64, 0, 0, 0};
+    float *vfe_w[4] = {nullptr, nullptr, nullptr, nullptr};    // [vfe_in][vfe_units], folded
+    float *vfe_b[4] = {nullptr, nullptr, nullptr, nullptr};
     gnd::ConvLayer conv[8];
     float *reg_w = nullptr;    // [9][64]
     float *reg_b = nullptr;    // [1]

@@ -563,6 +563,145 @@ __global__ void __launch_bounds__(PFN_WARPS * 32) pfn_scatter_dense_kernel(const
     }
 }
 
+// ---- multi-layer PillarFeatureNet (cfg.vfe_filters with more than one entry, modules/pointpillars.py:57-65, :96-107) ----
+// No shipped config uses it; this is the plain form: one warp per pillar, the per-slot feature rows of the current and
+// the next layer in shared memory.  A non-last PFNLayer has out / 2 units and hands concat(x, max over ALL max_points
+// slots) to the next layer; padded slots are zeroed only before the FIRST layer (:137-140), afterwards they carry
+// concat(relu(b'), max) like the reference's -- they are all equal, so one representative slot stands for them.
+struct PfnMulti {
+    int n_layers, cmax;
+    int cin[4], units[4];
+    const float *w[4], *b[4];
+};
+
+template <bool FUSED>
+__global__ void __launch_bounds__(32) pfn_multi_kernel(const PfnArgs a, const PfnMulti ml) {
+    extern __shared__ float s_rows[];                    // [2][P + 1][cmax]
+    const int lane = threadIdx.x;
+    const int cells = a.nx * a.ny;
+    const int64_t total = FUSED ? (int64_t)a.B * cells : a.M;
+    const bool vec4 = !FUSED && (a.F == 4) && ((((uintptr_t)a.points) & 15) == 0);
+    float *buf0 = s_rows, *buf1 = s_rows + (size_t)(a.P + 1) * ml.cmax;
+    for (int64_t m = blockIdx.x; m < total; m += gridDim.x) {
+        int b, n_real;
+        int64_t cell;
+        float nf, cxf, cyf;
+        const float *src;                                // rows of F (dense) or 4 (fused) floats
+        int stride;
+        if (FUSED) {
+            b = (int)(m / cells); cell = m - (int64_t)b * cells;
+            const int32_t *offc = a.offc + (int64_t)b * (cells + 1);
+            const int o = __ldg(offc + cell);
+            n_real = __ldg(offc + cell + 1) - o;
+            nf = (float)n_real;
+            cyf = (float)(cell / a.nx); cxf = (float)(cell - (cell / a.nx) * a.nx);
+            src = reinterpret_cast<const float *>(a.sorted + (int64_t)b * a.N + o); stride = 4;
+            if (n_real == 0) {                           // empty cell: zeros (the fused path has no memset)
+                for (int ch = lane; ch < PFN_OUT; ch += 32) {
+                    const int64_t o2 = ((int64_t)b * cells + cell) * PFN_OUT + ch;
+                    if (a.out32) a.out32[o2] = 0.0f;
+                    else { a.out_hi[o2] = __float2half_rn(0.0f); if (a.out_lo) a.out_lo[o2] = __float2half_rn(0.0f); }
+                }
+                continue;
+            }
+        } else {
+            nf = __ldg(a.num_f + m);
+            n_real = max(0, min(a.P, (int)nf));          // num_voxels.int() > arange (:202-223)
+            const float bf = __ldg(a.coors4 + m * 4 + 0);
+            cyf = __ldg(a.coors4 + m * 4 + 2); cxf = __ldg(a.coors4 + m * 4 + 3);
+            b = (int)bf;
+            cell = (int64_t)(__fadd_rn(__fmul_rn(cyf, (float)a.nx), cxf));
+            src = a.points + m * a.P * a.F; stride = a.F;
+        }
+        auto fetch = [&](int j, float &x, float &y, float &z, float &r) { load_point(src + (int64_t)j * stride, FUSED ? 4 : a.F, FUSED || vec4, x, y, z, r); };
+        // :120 points_mean: the dense tensor sums every slot (padded ones are zeros there), the fused path its kept points
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+        for (int j = lane; j < (FUSED ? n_real : a.P); j += 32) {
+            float x, y, z, r;
+            fetch(j, x, y, z, r);
+            sx += x; sy += y; sz += z;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            sx += __shfl_xor_sync(0xffffffffu, sx, d); sy += __shfl_xor_sync(0xffffffffu, sy, d); sz += __shfl_xor_sync(0xffffffffu, sz, d);
+        }
+        const float mx = __fdiv_rn(sx, nf), my = __fdiv_rn(sy, nf), mz = __fdiv_rn(sz, nf);
+        const float pcx = __fadd_rn(__fmul_rn(cxf, a.vx), a.xoff), pcy = __fadd_rn(__fmul_rn(cyf, a.vy), a.yoff);
+        const int slots = n_real + (n_real < a.P ? 1 : 0);
+        __syncwarp();
+        for (int j = lane; j < slots; j += 32) {
+            float *f = buf0 + (size_t)j * ml.cmax;
+            if (j < n_real) {
+                float x, y, z, r;
+                fetch(j, x, y, z, r);
+                int k = 0;
+                f[k++] = x; f[k++] = y; f[k++] = z;
+                if (a.F > 3) f[k++] = r;
+                f[k++] = __fsub_rn(x, mx); f[k++] = __fsub_rn(y, my); f[k++] = __fsub_rn(z, mz);
+                f[k++] = __fsub_rn(x, pcx); f[k++] = __fsub_rn(y, pcy);
+                if (a.with_distance) f[k++] = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+            } else {
+                for (int k = 0; k < a.nfeat; ++k) f[k] = 0.0f;      // the representative padded slot
+            }
+        }
+        __syncwarp();
+        float *in = buf0, *out = buf1;
+        for (int l = 0; l < ml.n_layers; ++l) {
+            const int C = ml.cin[l], U = ml.units[l];
+            const bool last = l == ml.n_layers - 1;
+            for (int ch = lane; ch < U; ch += 32) {
+                const float bias = __ldg(ml.b[l] + ch);
+                float vmax = -INFINITY;
+                for (int sidx = 0; sidx < slots; ++sidx) {
+                    const float *f = in + (size_t)sidx * ml.cmax;
+                    float y = bias;
+                    for (int k = 0; k < C; ++k) y = fmaf(__ldg(ml.w[l] + k * U + ch), f[k], y);
+                    y = fmaxf(y, 0.0f);
+                    if (!last) out[(size_t)sidx * ml.cmax + ch] = y;
+                    vmax = fmaxf(vmax, y);
+                }
+                if (last) {
+                    if (b >= 0 && b < a.B && cell >= 0 && cell < cells) {
+                        const int64_t o2 = ((int64_t)b * cells + cell) * PFN_OUT + ch;
+                        if (a.out32) a.out32[o2] = vmax;
+                        else {
+                            const __half h = __float2half_rn(vmax);
+                            a.out_hi[o2] = h;
+                            if (a.out_lo) a.out_lo[o2] = __float2half_rn(vmax - __half2float(h));
+                        }
+                    }
+                } else {
+                    for (int sidx = 0; sidx < slots; ++sidx) out[(size_t)sidx * ml.cmax + U + ch] = vmax;
+                }
+            }
+            __syncwarp();
+            float *t = in; in = out; out = t;
+        }
+    }
+}
+
+static int pfn_multi_run(gnd_ctx *ctx, PfnArgs &a, bool fused, int64_t total, cudaStream_t st) {
+    PfnMulti ml = {};
+    ml.n_layers = ctx->n_vfe;
+    ml.cmax = ctx->nfeat;
+    for (int l = 0; l < ctx->n_vfe; ++l) {
+        ml.cin[l] = ctx->vfe_in[l]; ml.units[l] = ctx->vfe_units[l];
+        ml.w[l] = ctx->vfe_w[l]; ml.b[l] = ctx->vfe_b[l];
+        if (ml.cin[l] > ml.cmax) ml.cmax = ml.cin[l];
+        if (l < ctx->n_vfe - 1 && 2 * ml.units[l] > ml.cmax) ml.cmax = 2 * ml.units[l];
+    }
+    const size_t smem = (size_t)2 * (a.P + 1) * ml.cmax * sizeof(float);
+    if (smem > 200 * 1024) return fail(GND_ERR_UNSUPPORTED, "multi-layer pillar encoder: %zu bytes of shared memory per pillar (max_points_voxel %d x %d features)", smem, a.P, ml.cmax);
+    if (fused) GND_CUDA_CHECK(cudaFuncSetAttribute(pfn_multi_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else GND_CUDA_CHECK(cudaFuncSetAttribute(pfn_multi_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = total < 148 * 16 ? total : 148 * 16;
+    if (blocks < 1) return GND_OK;
+    if (fused) pfn_multi_kernel<true><<<(int)blocks, 32, smem, st>>>(a, ml);
+    else pfn_multi_kernel<false><<<(int)blocks, 32, smem, st>>>(a, ml);
+    GND_LAUNCH_CHECK("pfn_multi_kernel");
+    return GND_OK;
+}
+
 static void fill_common(const gnd_ctx *ctx, PfnArgs &a, int32_t batch) {
     const gnd_config &c = ctx->cfg;
     a.B = batch;
@@ -633,6 +772,7 @@ int pfn_scatter_run(gnd_ctx *ctx, const float *points, int32_t batch, int64_t n_
     a.gshift = 3;
     while (a.gshift > 0 && (cells_all >> a.gshift) < 4 * 148 * 4 * PFN_WARPS) --a.gshift;
     if (tuning().pfn_gshift >= 0) a.gshift = tuning().pfn_gshift > 5 ? 5 : tuning().pfn_gshift;
+    if (ctx->n_vfe > 1) return pfn_multi_run(ctx, a, true, (int64_t)batch * ctx->nx * ctx->ny, st);
     if (!ctx->pfn_order) return fail(GND_ERR_STATE, "workspace has no work-unit order table");
     a.order = ctx->pfn_order + (size_t)a.gshift * ctx->nx * ctx->ny;
     int64_t warps = (cells_all + (1 << a.gshift) - 1) >> a.gshift;
@@ -666,6 +806,7 @@ int pfn_scatter_dense_run(gnd_ctx *ctx, const float *voxels, const float *coors4
     if (a.out_hi) GND_CUDA_CHECK(cudaMemsetAsync(a.out_hi, 0, n * sizeof(__half), st));
     if (a.out_lo) GND_CUDA_CHECK(cudaMemsetAsync(a.out_lo, 0, n * sizeof(__half), st));
     if (n_pillars == 0) return GND_OK;
+    if (ctx->n_vfe > 1) return pfn_multi_run(ctx, a, false, n_pillars, st);
     int blocks = (int)((n_pillars + PFN_WARPS - 1) / PFN_WARPS);
     if (blocks > 148 * 8) blocks = 148 * 8;
     pfn_scatter_dense_kernel<<<blocks, PFN_WARPS * 32, 0, st>>>(a);

@@ -67,6 +67,22 @@ extern "C" int gnd_create(const gnd_config *cfg, int32_t device, gnd_ctx **out) 
     ctx->H1 = ctx->ny / 2; ctx->W1 = ctx->nx / 2;
     ctx->H2 = ctx->H1 / 2; ctx->W2 = ctx->W1 / 2;
     ctx->nfeat = cfg->input_features + 5 + (cfg->with_distance ? 1 : 0);
+    {   // cfg.vfe_filters (modules/pointpillars.py:96-107)
+        int n = cfg->n_vfe == 0 ? 1 : cfg->n_vfe;
+        int f[GND_MAX_VFE] = {64, 0, 0, 0};
+        if (cfg->n_vfe != 0) for (int j = 0; j < GND_MAX_VFE; ++j) f[j] = cfg->vfe_filters[j];
+        bool ok = n >= 1 && n <= GND_MAX_VFE && f[n - 1] == PFN_OUT;
+        for (int j = 0; ok && j < n - 1; ++j) ok = f[j] >= 2 && f[j] <= 128 && (f[j] % 2) == 0;
+        if (!ok) { delete ctx; return fail(GND_ERR_UNSUPPORTED, "vfe_filters: 1..%d layers, the last one %d, the others even and <= 128", GND_MAX_VFE, PFN_OUT); }
+        if (n > 1 && cfg->bn_batch_stats) { delete ctx; return fail(GND_ERR_UNSUPPORTED, "batch-statistics mode with a multi-layer PillarFeatureNet"); }
+        ctx->n_vfe = n;
+        int cin = ctx->nfeat;
+        for (int j = 0; j < n; ++j) {
+            ctx->vfe_in[j] = cin;
+            ctx->vfe_units[j] = (j == n - 1) ? f[j] : f[j] / 2;
+            cin = f[j];
+        }
+    }
     for (int l = 0; l < 8; ++l) {
         ctx->conv[l].name = kBlocks[l].name;
         ctx->conv[l].cin = kBlocks[l].cin;
@@ -110,13 +126,16 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
         if (table[i].name) t.m[table[i].name] = &table[i];
     int rc = GND_OK;
     const bool tc = ctx->cfg.precision != GND_PREC_FP32;
-    const int nfeat = ctx->nfeat;
 
     // host staging of the whole blob
     size_t cur = 0;
     auto take = [&cur](size_t bytes) { cur = align_up(cur, 256); size_t r = cur; cur += bytes; return r; };
-    size_t o_pfn_w = take((size_t)nfeat * PFN_OUT * sizeof(float));
-    size_t o_pfn_b = take(PFN_OUT * sizeof(float));
+    size_t o_vfe_w[GND_MAX_VFE] = {0, 0, 0, 0}, o_vfe_b[GND_MAX_VFE] = {0, 0, 0, 0};
+    for (int l = 0; l < ctx->n_vfe; ++l) {
+        o_vfe_w[l] = take((size_t)ctx->vfe_in[l] * ctx->vfe_units[l] * sizeof(float));
+        o_vfe_b[l] = take((size_t)ctx->vfe_units[l] * sizeof(float));
+    }
+    const size_t o_pfn_w = o_vfe_w[0], o_pfn_b = o_vfe_b[0];      // one layer: [nfeat][64] + [64]
     size_t o_w[8], o_hi[8], o_lo[8], o_b[8], o_g[8], o_be[8];
     const bool batch_bn = ctx->cfg.bn_batch_stats != 0;
     for (int l = 0; l < 8; ++l) {
@@ -133,27 +152,29 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
     const size_t blob_bytes = align_up(cur, 256);
     std::vector<char> host(blob_bytes, 0);
 
-    // ---- PillarFeatureNet (modules/pointpillars.py:42-47) ----
-    {
-        const std::string pre = "voxel_feature_extractor.pfn_layers.0.";
-        const float *w = t.get(pre + "linear.weight", (int64_t)PFN_OUT * nfeat, &rc);
+    // ---- PillarFeatureNet (modules/pointpillars.py:42-47, :96-107): every PFNLayer's Linear, BatchNorm1d (eps 1e-3)
+    // folded when use_norm, stored input-major [cin][units] ----
+    for (int l = 0; l < ctx->n_vfe; ++l) {
+        const int cin = ctx->vfe_in[l], units = ctx->vfe_units[l];
+        const std::string pre = "voxel_feature_extractor.pfn_layers." + std::to_string(l) + ".";
+        const float *w = t.get(pre + "linear.weight", (int64_t)units * cin, &rc);
         if (!w) return rc;
-        float *dw = (float *)(host.data() + o_pfn_w), *db = (float *)(host.data() + o_pfn_b);
+        float *dw = (float *)(host.data() + o_vfe_w[l]), *db = (float *)(host.data() + o_vfe_b[l]);
         if (ctx->cfg.use_norm) {
-            const float *g = t.get(pre + "norm.weight", PFN_OUT, &rc);       if (!g) return rc;
-            const float *be = t.get(pre + "norm.bias", PFN_OUT, &rc);        if (!be) return rc;
-            const float *mu = t.get(pre + "norm.running_mean", PFN_OUT, &rc); if (!mu) return rc;
-            const float *var = t.get(pre + "norm.running_var", PFN_OUT, &rc); if (!var) return rc;
-            for (int ch = 0; ch < PFN_OUT; ++ch) {
+            const float *g = t.get(pre + "norm.weight", units, &rc);       if (!g) return rc;
+            const float *be = t.get(pre + "norm.bias", units, &rc);        if (!be) return rc;
+            const float *mu = t.get(pre + "norm.running_mean", units, &rc); if (!mu) return rc;
+            const float *var = t.get(pre + "norm.running_var", units, &rc); if (!var) return rc;
+            for (int ch = 0; ch < units; ++ch) {
                 double s = (double)g[ch] / sqrt((double)var[ch] + 1e-3);
-                for (int k = 0; k < nfeat; ++k) dw[k * PFN_OUT + ch] = (float)((double)w[ch * nfeat + k] * s);
+                for (int k = 0; k < cin; ++k) dw[k * units + ch] = (float)((double)w[ch * cin + k] * s);
                 db[ch] = (float)((double)be[ch] - (double)mu[ch] * s);
             }
         } else {
-            const float *b = t.get(pre + "linear.bias", PFN_OUT, &rc);
+            const float *b = t.get(pre + "linear.bias", units, &rc);
             if (!b) return rc;
-            for (int ch = 0; ch < PFN_OUT; ++ch) {
-                for (int k = 0; k < nfeat; ++k) dw[k * PFN_OUT + ch] = w[ch * nfeat + k];
+            for (int ch = 0; ch < units; ++ch) {
+                for (int k = 0; k < cin; ++k) dw[k * units + ch] = w[ch * cin + k];
                 db[ch] = b[ch];
             }
         }
@@ -205,6 +226,7 @@ extern "C" int gnd_load_weights(gnd_ctx *ctx, const gnd_weight *table, int32_t n
     char *d = (char *)ctx->weight_blob;
     ctx->pfn_w = (float *)(d + o_pfn_w);
     ctx->pfn_b = (float *)(d + o_pfn_b);
+    for (int l = 0; l < ctx->n_vfe; ++l) { ctx->vfe_w[l] = (float *)(d + o_vfe_w[l]); ctx->vfe_b[l] = (float *)(d + o_vfe_b[l]); }
     for (int l = 0; l < 8; ++l) {
         ctx->conv[l].w32 = tc ? nullptr : (float *)(d + o_w[l]);
         ctx->conv[l].whi = tc ? (__half *)(d + o_hi[l]) : nullptr;

@@ -37,6 +37,9 @@ class PFNLayer(nn.Module):
 
     def __init__(self, in_channels, out_channels, use_norm=True, last_layer=True):
         super().__init__()
+        if not last_layer:
+            out_channels = out_channels // 2            # :37-39: the other half is the pillar maximum, concatenated
+        self.units = out_channels
         if use_norm:
             self.linear = nn.Linear(in_channels, out_channels, bias=False)
             self.norm = nn.BatchNorm1d(out_channels, eps=1e-3, momentum=0.01)
@@ -51,10 +54,14 @@ class PillarFeatureNet(nn.Module):
     def __init__(self, num_input_features=4, use_norm=True, num_filters=(64,), with_distance=False,
                  voxel_size=(0.2, 0.2, 4), pc_range=(0, -40, -3, 70.4, 40, 1)):
         super().__init__()
-        if list(num_filters) != [64]:
-            raise NotImplementedError("vfe_filters must be [64] (every shipped config); got %r" % (num_filters,))
+        num_filters = [int(f) for f in num_filters]
+        if not (1 <= len(num_filters) <= 4) or num_filters[-1] != 64 or any(f < 2 or f > 128 or f % 2 for f in num_filters[:-1]):
+            raise ValueError("vfe_filters: 1..4 layers, the last one 64 (PointPillarsScatter and the segnet take 64 "
+                             "channels), the others even and <= 128; got %r" % (num_filters,))
         n_in = num_input_features + 5 + (1 if with_distance else 0)
-        self.pfn_layers = nn.ModuleList([PFNLayer(n_in, 64, use_norm, last_layer=True)])
+        filters = [n_in] + num_filters                  # pointpillars.py:96-107
+        self.pfn_layers = nn.ModuleList([PFNLayer(filters[i], filters[i + 1], use_norm, last_layer=(i == len(filters) - 2))
+                                         for i in range(len(filters) - 1)])
 
 
 class PointPillarsScatter(nn.Module):
@@ -161,6 +168,10 @@ class GroundEstimatorNet(nn.Module):
         c.with_distance = 1 if cfg.with_distance else 0
         c.precision = _lib.PRECISIONS[self.precision]
         c.bn_batch_stats = 1 if self.bn_mode == "batch" else 0
+        vf = [int(f) for f in cfg.vfe_filters]
+        c.n_vfe = len(vf)
+        for j, f in enumerate(vf):
+            c.vfe_filters[j] = f
         return c
 
     def _device(self):

@@ -207,16 +207,20 @@ def make_state_dict(cfg, seed=0, bn_stats=None):
     rng = np.random.default_rng(1000 + seed)
     sd = {}
     nin = cfg.input_features + 5 + (1 if cfg.with_distance else 0)
-    pre = "voxel_feature_extractor.pfn_layers.0."
-    sd[pre + "linear.weight"] = _u(rng, (64, nin), 0.4)
-    if cfg.use_norm:
-        sd[pre + "norm.weight"] = (0.75 + 0.5 * rng.random(64)).astype(np.float32)
-        sd[pre + "norm.bias"] = (0.1 * _gauss(rng, 64)).astype(np.float32)
-        sd[pre + "norm.running_mean"] = (2.0 * _gauss(rng, 64)).astype(np.float32)
-        sd[pre + "norm.running_var"] = (20.0 + 20.0 * rng.random(64)).astype(np.float32)
-        sd[pre + "norm.num_batches_tracked"] = np.array(1000, dtype=np.int64)
-    else:
-        sd[pre + "linear.bias"] = _u(rng, (64,), 0.3)
+    filters = [nin] + list(cfg.vfe_filters)                # pointpillars.py:96-107: non-last layers have out // 2 units
+    for i in range(len(filters) - 1):
+        last = i == len(filters) - 2
+        cin, units = filters[i], (filters[i + 1] if last else filters[i + 1] // 2)
+        pre = "voxel_feature_extractor.pfn_layers.%d." % i
+        sd[pre + "linear.weight"] = _u(rng, (units, cin), 0.4 if i == 0 else float(np.sqrt(6.0 / cin)))
+        if cfg.use_norm:
+            sd[pre + "norm.weight"] = (0.75 + 0.5 * rng.random(units)).astype(np.float32)
+            sd[pre + "norm.bias"] = (0.1 * _gauss(rng, units)).astype(np.float32)
+            sd[pre + "norm.running_mean"] = (2.0 * _gauss(rng, units)).astype(np.float32)
+            sd[pre + "norm.running_var"] = (20.0 + 20.0 * rng.random(units)).astype(np.float32)
+            sd[pre + "norm.num_batches_tracked"] = np.array(1000, dtype=np.int64)
+        else:
+            sd[pre + "linear.bias"] = _u(rng, (units,), 0.3)
     for name, cin, cout in CONV_BLOCKS:
         p = "encoder_decoder." + name + ".cbr_unit."
         b = float(np.sqrt(6.0 / (9 * cin)))

@@ -157,7 +157,12 @@ typedef struct gnd_config {
                                    the convolutions.  1: the module's TRAIN-mode arithmetic -- per-channel mean and
                                    biased variance of the batch being processed -- which is what predict_ground.py
                                    computes because it never calls .eval() (GND_PREC_FP32 only, use_norm = 0)   */
+    int32_t n_vfe;              /* len(cfg.vfe_filters), 1..GND_MAX_VFE; 0 is read as 1 layer of 64 (every shipped config) */
+    int32_t vfe_filters[4];     /* cfg.vfe_filters (modules/pointpillars.py:96-107): the last one must be 64 (the scatter
+                                   and the segnet take 64 channels), the others even and <= 128; non-last PFN layers have
+                                   out / 2 units and hand concat(x, max over the pillar) to the next layer              */
 } gnd_config;
+#define GND_MAX_VFE 4
 
 GND_API int gnd_create(const gnd_config *cfg, int32_t device, gnd_ctx **out);
 GND_API void gnd_destroy(gnd_ctx *ctx);

@@ -72,18 +72,22 @@ def pillar_feature_net(sd, cfg, voxels, num_points, coors):
     P = features.shape[1]
     mask = (num_voxels.int().unsqueeze(1) > torch.arange(P, dtype=torch.int, device=_DEV).view(1, -1))    # :202-223
     features = features * mask.unsqueeze(-1).to(features.dtype)                              # :137-140
-    pre = "voxel_feature_extractor.pfn_layers.0."
-    w = _t(sd[pre + "linear.weight"])
-    if getattr(cfg, "use_norm", False):
-        x = F.linear(features, w)                                                            # bias=False
-        x = F.batch_norm(x.permute(0, 2, 1).contiguous(), _t(sd[pre + "norm.running_mean"]),
-                         _t(sd[pre + "norm.running_var"]), _t(sd[pre + "norm.weight"]),
-                         _t(sd[pre + "norm.bias"]), False, 0.0, BN1D_EPS).permute(0, 2, 1).contiguous()
-    else:
-        x = F.linear(features, w, _t(sd[pre + "linear.bias"]))                               # :54
-    x = F.relu(x)
-    x_max = torch.max(x, dim=1, keepdim=True)[0]                                             # :58
-    return x_max.reshape(x_max.shape[0], -1)      # reference .squeeze() (M>=2) ; sane for M in {0,1}
+    n_layers = len(getattr(cfg, "vfe_filters", [64]))                                        # :96-107
+    for i in range(n_layers):
+        pre = "voxel_feature_extractor.pfn_layers.%d." % i
+        w = _t(sd[pre + "linear.weight"])
+        if getattr(cfg, "use_norm", False):
+            x = F.linear(features, w)                                                        # bias=False
+            x = F.batch_norm(x.permute(0, 2, 1).contiguous(), _t(sd[pre + "norm.running_mean"]),
+                             _t(sd[pre + "norm.running_var"]), _t(sd[pre + "norm.weight"]),
+                             _t(sd[pre + "norm.bias"]), False, 0.0, BN1D_EPS).permute(0, 2, 1).contiguous()
+        else:
+            x = F.linear(features, w, _t(sd[pre + "linear.bias"]))                           # :54
+        x = F.relu(x)
+        x_max = torch.max(x, dim=1, keepdim=True)[0]                                         # :58
+        if i == n_layers - 1:
+            return x_max.reshape(x_max.shape[0], -1)  # reference .squeeze() (M>=2) ; sane for M in {0,1}
+        features = torch.cat([x, x_max.repeat(1, P, 1)], dim=2)                              # :60-65 (padded slots included)
 
 
 def pillars_scatter(cfg, voxel_features, coors, batch_size):

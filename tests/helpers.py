@@ -138,8 +138,10 @@ def compare_heights(model, out, ref, st, precision=None):
                 flips=(n1, n2), tol=tol)
 
 
-def assert_heights(rep, precision, st, what=""):
-    """The height-parity claim, measurable: see the constants above."""
+def assert_heights(rep, precision, st, what="", tol_scale=1.0, max_frac_over=None):
+    """The height-parity claim, measurable: see the constants above.  ``tol_scale`` / ``max_frac_over`` loosen the bar /
+    the whole-map over-bar cap for checkpoints whose BatchNorm statistics were not calibrated for the model variant under
+    test (the multi-layer pillar encoders): every over-bar pixel still has to sit inside a flip neighbourhood."""
     line = ("%s %s: max|dh| outside flips=%.3g (bar %g)  over-bar pixels (unmasked map)=%.4f%%  masked=%.3f%%  "
             "overall max=%.3g  median=%.2g  argmax flips=%s" %
             (what, precision, rep["stable_max"], rep["tol"], 100 * rep["frac_over"], 100 * rep["frac_masked"],
@@ -149,9 +151,9 @@ def assert_heights(rep, precision, st, what=""):
     assert rep["flips"][0] <= 1e-4 * st["p1"].numel() + 2 and rep["flips"][1] <= 1e-4 * st["p2"].numel() + 2, "too many argmax flips: " + line
     m1, m2 = max_flips(st["out"].shape[0])
     assert rep["flips"][0] <= m1 and rep["flips"][1] <= m2, "too many argmax flips: " + line
-    assert rep["stable_max"] <= TOL[precision], line
+    assert rep["stable_max"] <= TOL[precision] * tol_scale, line
     k = _area_scale(st)
-    assert rep["frac_over"] <= MAX_FRAC_OVER[precision] * k, "too many pixels over the bar: " + line
+    assert rep["frac_over"] <= (MAX_FRAC_OVER[precision] if max_frac_over is None else max_frac_over) * k, "too many pixels over the bar: " + line
     assert rep["frac_masked"] <= MAX_FRAC_MASKED[precision] * k, "flip mask too large: " + line
     assert rep["overall"] <= MAX_OVERALL, line
 

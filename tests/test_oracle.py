@@ -114,3 +114,20 @@ def _raster_points(name):
     pts = synth.hdl64_scan(3)[:, :3].copy()
     pts[:, 2] += np.float32(1.733)
     return pts
+
+
+def test_multi_layer_pillar_feature_net_matches_reference_heights():
+    """cfg.vfe_filters with more than one entry (pointpillars.py:57-65, :96-107): the oracle against the unmodified
+    reference's outputs (oracle/ref_harness_vfe.py wrote tests/golden/model_heights_vfe.npz)."""
+    from oracle.ref_harness_vfe import VFE_CASES, case_key
+    with np.load(cases.GOLDEN + "/model_heights_vfe.npz") as z:
+        for cfgname, name, filters, use_norm in VFE_CASES:
+            cfg = synth.make_cfg(cfgname, batch_size=1, vfe_filters=filters, use_norm=use_norm)
+            sd = synth.make_state_dict(cfg, 0, synth.load_bn_stats(cfgname))
+            _, raw, _ = cases.load_case(name)
+            p = raw[:, :cfg.input_features].copy()
+            cpu_ops.shift_cloud(p, cfg.lidar_height)
+            v, c, n = cpu_ops.points_to_voxel(p, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+            c4 = np.concatenate([np.zeros((len(c), 1), np.float32), c.astype(np.float32)], 1)
+            out = model_ref.forward(sd, cfg, v, c4, n.astype(np.float32)).numpy()
+            assert np.abs(out - z[case_key(cfgname, name, filters, use_norm)]).max() <= 2e-5
