@@ -1339,6 +1339,7 @@ int vox_run_lean(const gnd_voxel_params *p, const VoxPlan &plan, const VoxWs &ws
     if (single) {
         // every CTA of a scan redoes the all-cells part: as few CTAs per scan as still fill the SMs
         int g = 148 / batch;
+        if (tuning().vox_g > 0) g = tuning().vox_g;
         a.G = g < 1 ? 1 : (g > 16 ? 16 : g);
         if (a.kc_shift) vl_cells1_kernel<true><<<batch * a.G, 1024, smem1, stream>>>(a);
         else vl_cells1_kernel<false><<<batch * a.G, 1024, smem1, stream>>>(a);
