@@ -167,6 +167,9 @@ extern "C" int gnd_set_option(gnd_ctx *ctx, const char *name, int32_t value) {
     } else if (!strcmp(name, "vox_path")) {
         if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "vox_path must be 0 (automatic), 1 (order-exact kernels) or 2 (set-exact kernels)");
         ctx->opt_vox_path = value;
+    } else if (!strcmp(name, "l2_order")) {
+        if (value < 0 || value > 1) return fail(GND_ERR_INVALID, "l2_order must be 0 (every kernel walks the scans forward) or 1 (alternating)");
+        ctx->opt_l2_order = value;
     } else if (!strcmp(name, "conv_geometry")) {
         if (value < 0 || value > 2) return fail(GND_ERR_INVALID, "conv_geometry must be 0 (auto), 1 (throughput) or 2 (small batch)");
         ctx->opt_conv_geom = value;

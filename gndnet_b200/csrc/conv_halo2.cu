@@ -70,6 +70,7 @@ struct Halo2Params {
     int SB, row0;
     uint32_t a_plane, a_stage, b_plane, b_stage, a_tx, b_tx;
     int half_items, pair_items;
+    int rev;                 // 1: items are walked from the last scan to the first
     const float *bias;
     __half *out_hi, *out_lo;
     const float *reg_w;
@@ -257,7 +258,8 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
         if (elect_one()) {
             // ===== halo producer (both CTAs): one box per (pair item, channel block), completion on the leader =====
             int sa = 0; uint32_t ph = 0;
-            for (int item = pair; item < p.pair_items; item += n_pairs) {
+            for (int it0 = pair; it0 < p.pair_items; it0 += n_pairs) {
+                const int item = p.rev ? p.pair_items - 1 - it0 : it0;     // scan order of this launch (see halo2_conv_run)
                 const Half it = h2_half(p, min(2 * (item / p.n_ntiles) + (int)rank, p.half_items - 1));
                 const int off = it.q0 - it.r_lo * p.Wp - 1;
                 for (int cb = 0; cb < p.cblocks; ++cb) {
@@ -275,7 +277,8 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
         if (elect_one()) {
             // ===== weight producer (both CTAs): this CTA's half of the NT rows per (pair item, channel block, tap) =====
             int sb = 0; uint32_t ph = 0;
-            for (int item = pair; item < p.pair_items; item += n_pairs) {
+            for (int it0 = pair; it0 < p.pair_items; it0 += n_pairs) {
+                const int item = p.rev ? p.pair_items - 1 - it0 : it0;     // scan order of this launch (see halo2_conv_run)
                 const int n0 = (item % p.n_ntiles) * p.NT + (int)rank * (p.NT / 2);
                 for (int cb = 0; cb < p.cblocks; ++cb)
                     for (int tap = 0; tap < 9; ++tap) {
@@ -300,7 +303,8 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
             long long st[4] = {0, 0, 0, 0}; const long long tstart = clock64();
             atomicAdd(&g_h2_stats[4], (unsigned long long)(tstart - t_entry));      // prologue: entry -> issuer ready
 #endif
-            for (int item = pair; item < p.pair_items; item += n_pairs) {
+            for (int it0 = pair; it0 < p.pair_items; it0 += n_pairs) {
+                const int item = p.rev ? p.pair_items - 1 - it0 : it0;     // scan order of this launch (see halo2_conv_run)
                 const int j = item / p.n_ntiles;
                 const int tiles = max(h2_half(p, min(2 * j, p.half_items - 1)).tiles, h2_half(p, min(2 * j + 1, p.half_items - 1)).tiles);
                 { H2T0(); mbar_wait_cluster(bar_tempty + 8 * acc, phacc ^ 1); H2ADD(0); }
@@ -339,7 +343,8 @@ conv3x3_halo2_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_c
         const int qd = warp & 3;
         const int row = qd * 32 + lane;
         int acc = 0; uint32_t phacc = 0;
-        for (int item = pair; item < p.pair_items; item += n_pairs) {
+        for (int it0 = pair; it0 < p.pair_items; it0 += n_pairs) {
+                const int item = p.rev ? p.pair_items - 1 - it0 : it0;     // scan order of this launch (see halo2_conv_run)
             const Half it = h2_half(p, min(2 * (item / p.n_ntiles) + (int)rank, p.half_items - 1));
             const int n0 = (item % p.n_ntiles) * p.NT;
             mbar_wait(bar_tfull + 8 * acc, phacc);
@@ -574,6 +579,11 @@ int halo2_conv_run(gnd_ctx *ctx, int l, const Act &out, int B, bool fuse_regress
     p.B = B;
     p.half_items = B * p.strips * p.groups;
     p.pair_items = ((p.half_items + 1) / 2) * p.n_ntiles;
+    // L2 reuse across launches: a kernel that walks the scans in the REVERSE order of its producer finds the producer's
+    // last-written scans still in the 126 MB L2 (write-back) instead of fetching them from HBM.  The chain alternates:
+    // down1.conv1 forward, down1.conv2 reverse, pool forward, down2.conv1 reverse, down2.conv2 forward, pool+mask
+    // reverse, up2.conv1 forward, up2.conv2 reverse, unpool forward, up1.conv1 reverse, up1.conv2 forward
+    p.rev = (ctx->opt_l2_order && (l == 1 || l == 2 || l == 5 || l == 6)) ? 1 : 0;
     p.out_hi = fuse_regressor ? nullptr : out.hi;
     p.out_lo = fuse_regressor ? nullptr : out.lo;
     p.reg_w = ctx->reg_w;

@@ -87,6 +87,7 @@ struct gnd_ctx {
     // gnd_set_option
     int opt_conv_path = 0;      // 0: CTA-pair halo kernel (conv_halo2.cu) where it fits, 1: single-CTA tap kernel (conv_tc.cu)
     int opt_conv_geom = 0;      // 0: automatic, 1: throughput geometry, 2: small-batch geometry
+    int opt_l2_order = 0;       // 1: consecutive segnet kernels walk the scans in alternating directions (L2 reuse), 0: all forward (default: no gain measured)
     int opt_pfn_path = 0;       // fused pillar encoder: 0: automatic (= the CUDA-core kernel: measured faster), 1: CUDA-core kernel, 2: mma.sync (TF32 x3) kernel
     int opt_vox_path = 0;       // gnd_infer: 0: automatic (set-exact voxelization unless the cloud is dense), 1: order-exact kernels, 2: set-exact
 

@@ -159,13 +159,14 @@ __global__ void __launch_bounds__(256) pool_h8_kernel(const Act in, const Act ou
 }
 
 // one thread per (2x2 window incl. partial border windows, 8 channels)
-__global__ void __launch_bounds__(256) pool_mask_h8_kernel(const Act in, const Act out, int B) {
+__global__ void __launch_bounds__(256) pool_mask_h8_kernel(const Act in, const Act out, int B, int rev) {
     const int C8 = in.C / 8, H = in.H, W = in.W, Hp = H / 2, Wp = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2;
     const size_t total = (size_t)B * Hc * Wc * C8;
     H8 zero;
 #pragma unroll
     for (int k = 0; k < 8; ++k) zero.v[k] = 0.0f;
-    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < total; g += (size_t)gridDim.x * 256) {
+    for (size_t g0 = (size_t)blockIdx.x * 256 + threadIdx.x; g0 < total; g0 += (size_t)gridDim.x * 256) {
+        const size_t g = rev ? total - 1 - g0 : g0;        // last scan first: its rows are the ones the conv before left in L2
         const int c = (int)(g % C8) * 8;
         size_t p = g / C8;
         const int wc = (int)(p % Wc); p /= Wc;
@@ -472,7 +473,7 @@ int segnet_run(gnd_ctx *ctx, int32_t B, float *height, cudaStream_t st, cudaEven
     GND_LAUNCH_CHECK("pool_kernel");
     CONV(2, ctx->p1, ctx->d2a, false);
     CONV(3, ctx->d2a, ctx->d2b, false);
-    if (tc) pool_mask_h8_kernel<<<ew_blocks(ctx->u2.elems(B) / 32 + 1), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
+    if (tc) pool_mask_h8_kernel<<<ew_blocks(ctx->u2.elems(B) / 32 + 1), 256, 0, st>>>(ctx->d2b, ctx->u2, B, ctx->opt_l2_order);
     else pool_mask_kernel<<<ew_blocks(ctx->u2.elems(B)), 256, 0, st>>>(ctx->d2b, ctx->u2, B);
     GND_LAUNCH_CHECK("pool_mask_kernel");
     CONV(4, ctx->u2, ctx->u2a, false);

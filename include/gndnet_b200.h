@@ -296,6 +296,9 @@ GND_API int gnd_last_launch_count(const gnd_ctx *ctx);
 /* Per-ctx switches (tests, A/B timing; never read from the environment at launch time):
  *   "conv_path"      0 = CTA-pair halo kernel where the shape fits (default), 1 = single-CTA tap kernel (the fallback)
  *   "conv_geometry"  0 = automatic, 1 = throughput geometry, 2 = small-batch geometry of the pair kernel
+ *   "l2_order"       0 (default) = every segnet kernel walks the scans of a batch forward, 1 = consecutive kernels walk
+ *                    them in alternating directions, so that a kernel starts on the scans its producer wrote last
+ *                    (A/B switch: no step-time difference was measured).  Same results bit for bit.
  *   "pfn_path"       fused pillar encoder: 0 = automatic (default; today the CUDA-core kernel: 0.21 ms against 0.24 ms per
  *                    64 scans), 1 = CUDA-core kernel, 2 = mma.sync TF32x3 kernel (cfg.with_distance == 0 only; else the
  *                    CUDA-core kernel runs)

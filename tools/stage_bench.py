@@ -16,6 +16,7 @@ ap.add_argument("--cfg", default="kitti")
 ap.add_argument("--pfn-path", type=int, default=None)
 ap.add_argument("--vox-path", type=int, default=None)
 ap.add_argument("--conv-geometry", type=int, default=None)
+ap.add_argument("--l2-order", type=int, default=None)
 ap.add_argument("--tag", default="")
 args = ap.parse_args()
 cfg = synth.make_cfg(args.cfg)
@@ -23,7 +24,7 @@ sd, _ = synth.checkpoint(args.cfg)
 model = GroundEstimatorNet(cfg, precision=args.precision)
 model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
 model = model.cuda().eval()
-for name in ("pfn_path", "vox_path", "conv_geometry"):
+for name in ("pfn_path", "vox_path", "conv_geometry", "l2_order"):
     v = getattr(args, name)
     if v is not None:
         model.set_option(name, v)
