@@ -16,6 +16,7 @@ ap.add_argument("--steps", type=int, default=2)
 ap.add_argument("--precision", default="mixed")
 ap.add_argument("--cfg", default="kitti")
 ap.add_argument("--pfn-path", type=int, default=None, help="1: CUDA-core pillar encoder, 2: mma.sync one")
+ap.add_argument("--l2-order", type=int, default=None, help="1: segnet kernels walk the scans in alternating directions")
 ap.add_argument("--vox-path", type=int, default=0, help="1: order-exact voxelizer kernels inside infer()")
 args = ap.parse_args()
 cfg = synth.make_cfg(args.cfg)
@@ -25,6 +26,8 @@ model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()
 model = model.cuda().eval()
 if args.pfn_path is not None:
     model.set_option("pfn_path", args.pfn_path)
+if args.l2_order is not None:
+    model.set_option("l2_order", args.l2_order)
 if args.vox_path:
     model.set_option("vox_path", args.vox_path)
 base = [synth.hdl64_scan(s) if args.cfg == "kitti" else synth.camera_scan(s) for s in range(4)]
