@@ -64,6 +64,7 @@ _SIGS = {
     "gnd_segment_cloud": (ctypes.c_int, [ctypes.POINTER(SegmentParams), c_vp, c_vp, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "gnd_compact_workspace_bytes": (ctypes.c_int, [c_i64, ctypes.POINTER(c_sz)]),
     "gnd_compact_obstacles": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i32, c_vp, c_sz, c_vp, c_vp, c_vp]),
+    "gnd_compact_obstacles_static": (ctypes.c_int, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "gnd_create": (ctypes.c_int, [ctypes.POINTER(Config), c_i32, ctypes.POINTER(c_vp)]),
     "gnd_destroy": (None, [c_vp]),
     "gnd_load_weights": (ctypes.c_int, [c_vp, ctypes.POINTER(Weight), c_i32]),

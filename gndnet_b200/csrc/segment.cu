@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include <limits.h>
 #include <math.h>
+#include <atomic>
 
 namespace gnd {
 
@@ -189,6 +190,70 @@ extern "C" int gnd_compact_obstacles(const int8_t *labels_i8, const float *point
     if (!workspace || workspace_bytes < need) return fail(GND_ERR_WORKSPACE, "compaction workspace: need %zu bytes", need);
     int nblocks = (int)((n_points + CMP_BLOCK - 1) / CMP_BLOCK);
     int32_t *bc = (int32_t *)workspace;
+    compact_count_kernel<<<nblocks, CMP_BLOCK, 0, st>>>(labels_i8, n_points, bc);
+    GND_LAUNCH_CHECK("compact_count_kernel");
+    compact_scan_kernel<<<1, 1024, 0, st>>>(bc, nblocks, obstacle_count);
+    GND_LAUNCH_CHECK("compact_scan_kernel");
+    compact_write_kernel<<<nblocks, CMP_BLOCK, 0, st>>>(labels_i8, points_obstacle, n_points, obstacle_features, bc, out_obstacle);
+    GND_LAUNCH_CHECK("compact_write_kernel");
+    return GND_OK;
+}
+
+// ---- obstacle compaction for callers that cannot allocate device memory -------------------------------------------
+// gnd_compact_obstacles_static is gnd_compact_obstacles without the caller-provided workspace.  Who needs it: code that
+// is handed device buffers it does not own and has no allocator of its own to ask for the few KB of block counters --
+// a publisher callback running inside someone else's memory pool, a plug-in loaded into a process whose device memory
+// is fully pre-partitioned at start-up, a real-time loop whose rules forbid cudaMalloc (it synchronises the device and
+// can take milliseconds).  The per-block counters live in the library image instead: one fixed array per GPU, there from
+// the moment the library is loaded on that GPU until the process exits.
+//
+// g_compact_static is a DEVICE array.  In the host functions below its name is only a handle for the runtime's symbol
+// table, never a pointer a kernel may be given; the device address is asked for once per GPU with cudaGetSymbolAddress
+// (while that GPU is current) and cached in g_compact_static_addr[device].
+constexpr int64_t CMP_STATIC_MAX_POINTS = GND_COMPACT_STATIC_MAX_POINTS;
+constexpr int CMP_STATIC_SLOTS = (int)(CMP_STATIC_MAX_POINTS / CMP_BLOCK) + 1;    // one counter per 1024 labels (+1 spare)
+static_assert(CMP_STATIC_MAX_POINTS % CMP_BLOCK == 0, "the limit is a whole number of compaction blocks");
+static __device__ __align__(256) int32_t g_compact_static[CMP_STATIC_SLOTS];       // 16 KB + 4 B per GPU
+
+constexpr int CMP_STATIC_MAX_DEVICES = 64;
+static std::atomic<int32_t *> g_compact_static_addr[CMP_STATIC_MAX_DEVICES];
+
+// Device address of g_compact_static on the CURRENT device (looked up on the first call per device, then cached).
+static int compact_static_scratch(int32_t **out) {
+    int dev = -1;
+    GND_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= CMP_STATIC_MAX_DEVICES) return gnd::fail(GND_ERR_UNSUPPORTED, "device ordinal %d >= %d", dev, CMP_STATIC_MAX_DEVICES);
+    int32_t *p = g_compact_static_addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        void *sym = nullptr;
+        GND_CUDA_CHECK(cudaGetSymbolAddress(&sym, g_compact_static));
+        if (!sym) return gnd::fail(GND_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the compaction scratch");
+        p = (int32_t *)sym;
+        g_compact_static_addr[dev].store(p, std::memory_order_release);   // two threads racing here store the same value
+    }
+    *out = p;
+    return GND_OK;
+}
+
+extern "C" int gnd_compact_obstacles_static(const int8_t *labels_i8, const float *points_obstacle, int64_t n_points,
+                                            int32_t obstacle_features, float *out_obstacle, int32_t *obstacle_count,
+                                            void *stream) {
+    g_launches = 0;
+    if (n_points < 0 || obstacle_features < 1) return fail(GND_ERR_INVALID, "bad shape");
+    if (n_points > CMP_STATIC_MAX_POINTS)
+        return fail(GND_ERR_UNSUPPORTED,
+                    "gnd_compact_obstacles_static handles at most %lld points per call (got %lld): split the cloud or use "
+                    "gnd_compact_obstacles with a workspace of your own",
+                    (long long)CMP_STATIC_MAX_POINTS, (long long)n_points);
+    if (!obstacle_count) return fail(GND_ERR_INVALID, "obstacle_count is null");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_points == 0) { GND_CUDA_CHECK(cudaMemsetAsync(obstacle_count, 0, sizeof(int32_t), st)); return GND_OK; }
+    if (!labels_i8 || !points_obstacle || !out_obstacle) return fail(GND_ERR_INVALID, "null pointer");
+    int32_t *bc = nullptr;
+    if (int rc = compact_static_scratch(&bc)) return rc;
+    // Nothing in the scratch has to start at zero: the count kernel overwrites counters [0, nblocks) and the two
+    // kernels after it read only those, so whatever an earlier call left behind is never seen.
+    const int nblocks = (int)((n_points + CMP_BLOCK - 1) / CMP_BLOCK);
     compact_count_kernel<<<nblocks, CMP_BLOCK, 0, st>>>(labels_i8, n_points, bc);
     GND_LAUNCH_CHECK("compact_count_kernel");
     compact_scan_kernel<<<1, 1024, 0, st>>>(bc, nblocks, obstacle_count);

@@ -133,6 +133,30 @@ GND_API int gnd_compact_obstacles(const int8_t *labels_i8, const float *points_o
                                   int32_t obstacle_features, void *workspace, size_t workspace_bytes,
                                   float *out_obstacle, int32_t *obstacle_count, void *stream);
 
+/*
+ * gnd_compact_obstacles for callers that have no way to provide the workspace.  (No counterpart in the reference:
+ * numpy allocates wherever it likes.  This exists for the deployment side only.)
+ *
+ * Some users of this library are handed device buffers but cannot create one: a callback running inside another
+ * component's memory pool, a plug-in in a process whose GPU memory was carved up completely at start-up, a real-time
+ * loop in which cudaMalloc is banned because it stalls the whole device.  For them the block counters the compaction
+ * needs sit in a fixed array inside the library image (16 KB, present on every GPU that loads the library, for the
+ * life of the process).  The call itself allocates and frees nothing, on the host or the device.
+ *
+ * Same arguments and results as gnd_compact_obstacles minus workspace / workspace_bytes.  Differences to know about:
+ *   - n_points may not exceed GND_COMPACT_STATIC_MAX_POINTS; a larger cloud is refused with GND_ERR_UNSUPPORTED (split
+ *     it, or use gnd_compact_obstacles);
+ *   - the first call on each GPU looks up the array's device address (a one-off runtime query, made with that GPU
+ *     current).  Make that first call during set-up, outside any stream capture;
+ *   - every call on a GPU uses the SAME array.  Two calls whose kernels can overlap on that GPU (different streams,
+ *     different threads) corrupt each other's counters: run them on one stream or order them with events.  Calls on
+ *     different GPUs are independent.  The array keeps the previous call's values; the call does not depend on them.
+ */
+#define GND_COMPACT_STATIC_MAX_POINTS 4194304   /* 4 Mi points per call */
+GND_API int gnd_compact_obstacles_static(const int8_t *labels_i8, const float *points_obstacle, int64_t n_points,
+                                         int32_t obstacle_features, float *out_obstacle, int32_t *obstacle_count,
+                                         void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * Model context.  Replaces model.py:13-42 GroundEstimatorNet (+ modules/pointpillars.py,
  * modules/segnet.py) in eval mode, and predict_ground.py:110-121,165-168 InferGround +
