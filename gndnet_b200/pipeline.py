@@ -240,20 +240,37 @@ def rate_shards(rates, total, lo, hi):
     r = np.asarray(rates, dtype=np.float64)
     if len(r) < 1 or not np.all(np.isfinite(r)) or np.any(r <= 0) or lo * len(r) > total or hi * len(r) < total:
         raise ValueError("bad shard request: rates=%r total=%d bounds=[%d, %d]" % (list(rates), total, lo, hi))
-    want = np.clip(total * r / r.sum(), lo, hi)
-    want *= total / want.sum()
-    base = np.clip(np.floor(want).astype(int), lo, hi)
+    # water-filling: ranks whose proportional share falls outside [lo, hi] are pinned to the bound, the rest share what
+    # is left in proportion to their rates, until no share violates a bound (at most len(r) rounds)
+    want = np.zeros(len(r))
+    free = np.ones(len(r), dtype=bool)
+    left = float(total)
+    while free.any():
+        share = left * r / r[free].sum()
+        under, over = free & (share < lo), free & (share > hi)
+        if not under.any() and not over.any():
+            want[free] = share[free]
+            break
+        # pin the side that is further out of bounds first; the other side is re-examined with the new remainder
+        pin_lo = (lo - share[under]).sum() >= (share[over] - hi).sum()
+        pin, bound = (under, lo) if pin_lo else (over, hi)
+        want[pin] = bound
+        free &= ~pin
+        left -= bound * int(pin.sum())
+    base = np.clip(np.floor(want + 1e-9).astype(int), lo, hi)
     rem = total - int(base.sum())
     order = np.argsort(-(want - base), kind="stable")
-    i = 0
-    while rem != 0 and i < 10 * len(r):
-        k = order[i % len(r)]
+    # the rounding remainder goes out one scan at a time, largest fraction first, over the ranks that are not at a
+    # bound; the request fails only when no rank can take (or give) another scan
+    while rem != 0:
         step = 1 if rem > 0 else -1
-        if lo <= base[k] + step <= hi:
-            base[k] += step
-            rem -= step
-        i += 1
-    if rem != 0:
-        raise ValueError("cannot place %d scans within [%d, %d] per rank" % (total, lo, hi))
+        moved = False
+        for k in (order if step > 0 else order[::-1]):
+            if rem != 0 and lo <= base[k] + step <= hi:
+                base[k] += step
+                rem -= step
+                moved = True
+        if not moved:
+            raise ValueError("cannot place %d scans within [%d, %d] per rank" % (total, lo, hi))
     return [int(x) for x in base]
 

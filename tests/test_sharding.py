@@ -31,6 +31,15 @@ def test_rate_shards_follow_the_link_rates():
     assert rate_shards([55.4, 55.4], 128, 32, 128) == [64, 64]           # equal links: equal shards
     assert rate_shards([1.0, 100.0], 128, 32, 128) == [32, 96]           # the bounds hold
     assert rate_shards([3.0], 64, 8, 128) == [64]
+    # a skewed but feasible request: the fast rank clips at the upper bound, the slow one takes the rest
+    assert rate_shards([1.0, 100.0], 128, 16, 100) == [28, 100]
+    assert rate_shards([1.0, 1.0, 100.0], 200, 10, 100) == [50, 50, 100]
+    assert rate_shards([1.0, 50.0, 50.0], 100, 20, 60) == [20, 40, 40]
+    for rates, total, lo, hi in ([[1.0, 2.0, 4.0, 8.0, 16.0, 32.0, 64.0, 128.0], 512, 32, 128], [[5.0, 1.0, 1.0], 96, 32, 32],
+                                 [[1e-3, 1e3], 65, 1, 64]):
+        s = rate_shards(rates, total, lo, hi)
+        assert sum(s) == total and min(s) >= lo and max(s) <= hi
+        assert all(s[i] <= s[j] for i in range(len(s)) for j in range(len(s)) if rates[i] < rates[j])   # monotone in the rate
     for bad in ([], [1.0, 0.0], [1.0, float("nan")]):
         with pytest.raises(ValueError):
             rate_shards(bad, 128, 32, 128)
