@@ -136,6 +136,7 @@ class GroundEstimatorNet(nn.Module):
         self._ctx = None
         self._ctx_device = None
         self._weights_version = None
+        self._weights_epoch = 0
         self._ws = None
         self._bound = None
         self._warned_train = False
@@ -186,11 +187,21 @@ class GroundEstimatorNet(nn.Module):
         # modules' dicts (the module tree is fixed, the tensor objects are not): catches load_state_dict (in place),
         # load_state_dict(assign=True), re-assigned Parameters and dtype / device moves.  ~60 dict lookups, a few
         # microseconds -- it sits on the batch-1 latency path (state_dict() here cost ~75 us per call).
+        # NOT caught: writes that go through ``p.data`` (p.data.copy_(w), p.data.add_(g) -- the idiom of the reference's
+        # torchplus/train/optim.py:110).  ``.data`` is a detached alias with a version counter of its own, so neither
+        # id(p) nor p._version moves.  After such a write call invalidate_weights(); the epoch below then changes.
         if self._slots is None:
             # batch-statistics mode never reads the BatchNorm2d running buffers (and updates them after every call)
             skip = (lambda m, d: self.bn_mode == "batch" and isinstance(m, nn.BatchNorm2d) and d is m._buffers)
             self._slots = [(d, n) for m in self.modules() for d in (m._parameters, m._buffers) for n in d if not skip(m, d)]
-        return tuple((id(t), t._version) for t in (d[n] for d, n in self._slots) if t is not None)
+        return (self._weights_epoch,) + tuple((id(t), t._version) for t in (d[n] for d, n in self._slots) if t is not None)
+
+    def invalidate_weights(self):
+        """Tell the model that parameters or buffers were written behind autograd's back (``p.data.copy_(...)``,
+        ``p.data.add_(...)``, a raw pointer write): such writes do not bump ``Tensor._version``, so the automatic check
+        cannot see them and the device copy of the folded weights would stay as it was.  The next forward() / infer()
+        folds and uploads them again; ScanStream drops its captured graphs and a GraphedInfer refuses to replay."""
+        self._weights_epoch += 1
 
     def _ensure_ctx(self, defer_version_check=False):
         """``defer_version_check``: the latency path (infer) compares the parameter versions AFTER its launches are
@@ -490,8 +501,11 @@ class GroundEstimatorNet(nn.Module):
     def pillars(self, batch):
         """Voxelizer outputs of the last infer() as tensors (views of the workspace): coors, num_points, voxel_count,
         point_offsets, and the kept points grouped by CELL (cell_offsets [B, cells + 1], cell_points [B, N, 4]).
-        ``point_list`` (per-pillar point indices in slot order) is filled only when the order-exact voxelizer ran
-        (``set_option("vox_path", 1)``, or the stage / drop-in APIs): the fused path keeps sets, not slot order."""
+        ``point_list`` (per-pillar point indices in slot order) and ``point_offsets[b, :M]`` (their per-pillar CSR
+        offsets) are filled only when the order-exact voxelizer ran (``set_option("vox_path", 1)``, or the stage /
+        drop-in APIs): the fused path keeps sets, not slot order, and writes just ``point_offsets[b, M]`` -- the number
+        of kept points of scan b, M = voxel_count[b].  Entries below M are then stale (or uninitialised) and must not be
+        read; per-pillar sizes are ``num_points``, per-cell groups are ``cell_offsets`` / ``cell_points``."""
         mv = int(getattr(self.cfg, "max_voxels", self.nx * self.ny * self.nz))
         Bb = self._bound[0]
         N = self._last_n                     # row stride of the per-point buffers = the n_points of that call

@@ -242,7 +242,9 @@ GND_API int gnd_segment(gnd_ctx *ctx, const float *points, const int32_t *counts
                         double *labels_f64, void *stream);
 /* Stages 1-4 back to back on `stream`.  The voxelization inside is set-exact (see gnd_set_option "vox_path"): pillar
  * ids, coors, num_points and every pillar's kept points equal the reference's; the per-pillar point index lists in
- * slot order are only materialised by gnd_voxelize / gnd_points_to_voxel. */
+ * slot order ("point_list") and their offsets ("point_offsets" rows [0, M)) are only materialised by gnd_voxelize /
+ * gnd_points_to_voxel.  After a set-exact run the workspace's "point_offsets" holds ONE valid entry per scan, row
+ * M = voxel_count[b] (the number of kept points); the rows below it are stale or uninitialised. */
 GND_API int gnd_infer(gnd_ctx *ctx, const float *points, const int32_t *counts, int32_t batch,
                       int64_t n_points, double threshold, float *height, int8_t *labels_i8,
                       double *labels_f64, void *stream);

@@ -20,9 +20,9 @@ def _available_precisions():
     return ["fp32", "mixed", "split"]
 
 
-def _run_case(cfgname, scans, overrides, precision, device):
+def _run_case(cfgname, scans, overrides, precision, device, seed=0):
     cfg = synth.make_cfg(cfgname, batch_size=len(scans), **overrides)
-    model, sd = helpers.load_model(cfg, cfgname, precision, device)
+    model, sd = helpers.load_model(cfg, cfgname, precision, device, seed=seed)
     raws = [cases.load_case(s)[1] for s in scans]
     v, c, n, shifted = helpers.oracle_pillars(cfg, raws)
     ref, st = model_ref.forward(sd, cfg, v, c, n, return_stages=True)
@@ -102,7 +102,22 @@ def test_fused_infer_end_to_end(cfgname, scans, overrides, precision, cuda):
     """Raw scans -> infer() -> height + labels, against the oracle's full reference call sequence
     (predict_ground.py:110-121, :165-168) -- including the dense 1 M-point camera frame (every pillar truncated at
     max_points, odd 25 -> 12 pooling) and scans whose voxelization hits the max_voxels break."""
-    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, scans, overrides, precision, cuda)
+    _fused_infer_case(cfgname, scans, overrides, precision, cuda, seed=0)
+
+
+@pytest.mark.parametrize("precision", _available_precisions())
+@pytest.mark.parametrize("seed", [1, 2])
+@pytest.mark.parametrize("cfgname,scans", [("kitti", ["hdl64_s0", "real_000000"]), ("camera", ["small_camera"])])
+def test_fused_infer_other_weight_draws(cfgname, scans, seed, precision, cuda):
+    """The same end-to-end claim on two more draws of the weights (seeds 1 and 2, BatchNorm statistics calibrated per
+    draw with the recipe of the committed seed-0 checkpoint): the bars and the flip allowances are not tuned to one
+    state_dict.  No reference goldens exist for these draws; the oracle -- pinned to the reference on seed 0 -- is the
+    checker."""
+    _fused_infer_case(cfgname, scans, {}, precision, cuda, seed=seed)
+
+
+def _fused_infer_case(cfgname, scans, overrides, precision, cuda, seed):
+    cfg, model, sd, raws, (v, c, n), shifted, ref, st = _run_case(cfgname, scans, overrides, precision, cuda, seed=seed)
     nmax = max(len(r) for r in raws)
     F = cfg.input_features
     batch = np.full((len(raws), nmax, F), 1e9, dtype=np.float32)
@@ -122,7 +137,7 @@ def test_fused_infer_end_to_end(cfgname, scans, overrides, precision, cuda):
         assert np.array_equal(pil["num_points"][b, :m], n[ofs:ofs + m].astype(np.int32))
         ofs += m
     helpers.assert_heights(helpers.compare_heights(model, height, ref, st), precision, st,
-                           "infer %s %s" % (cfgname, "+".join(scans)))
+                           "infer %s %s%s" % (cfgname, "+".join(scans), "" if seed == 0 else " seed%d" % seed))
     refn = ref.numpy().reshape(len(raws), model.ny, model.nx)
     total = same = 0
     for b, p in enumerate(shifted):
@@ -360,13 +375,12 @@ def test_multi_layer_pillar_feature_net(case, precision, cuda):
     assert dc <= 2e-5 * scale, "forward: canvas differs by %g" % dc
     # the synthetic checkpoint's BatchNorm2d statistics were calibrated for the one-layer encoder: with these encoders the
     # activations are larger, the fp16 decoder's error with them (mixed: up to 5.3e-3 m) and near-ties more frequent
-    loose = dict(tol_scale=2.0 if precision == "mixed" else 1.0, max_frac_over=helpers.MAX_FRAC_MASKED[precision])
-    helpers.assert_heights(helpers.compare_heights(model, out, ref, st), precision, st, "multi-layer PFN forward %s" % (filters,), **loose)
+    helpers.assert_heights(helpers.compare_heights(model, out, ref, st), precision, st, "multi-layer PFN forward %s" % (filters,))
     with torch.no_grad():
         h, lab = model.infer(torch.from_numpy(np.ascontiguousarray(raw[:, :cfg.input_features])).cuda(), threshold=0.08, labels="int8")
     dc = (canvas() - st["canvas"]).abs().max().item()
     assert dc <= 2e-5 * scale, "infer: canvas differs by %g" % dc
-    helpers.assert_heights(helpers.compare_heights(model, h, ref, st), precision, st, "multi-layer PFN infer %s" % (filters,), **loose)
+    helpers.assert_heights(helpers.compare_heights(model, h, ref, st), precision, st, "multi-layer PFN infer %s" % (filters,))
     exp = cpu_ops.segment_cloud(shifted[0].copy(), np.asarray(cfg.grid_range), cfg.voxel_size[0], ref.numpy().reshape(model.ny, model.nx).T, 0.08)
     assert float((lab.cpu().numpy().astype(np.float64) == exp).mean()) >= 0.999
     model.release()

@@ -204,6 +204,19 @@ def test_replaced_parameters_are_re_uploaded(cuda):
         model.encoder_decoder.regressor.bias.sub_(0.75)                     # in place: the _version path
         h3, _ = model.infer(pts, labels=None)
         assert torch.allclose(h3, h0, atol=1e-6)
+        # writes through .data (torchplus/train/optim.py:110 in the reference) move neither id() nor _version: the
+        # documented limitation, and invalidate_weights() is the way out
+        bias = model.encoder_decoder.regressor.bias
+        v = bias._version
+        bias.data.add_(0.125)
+        assert bias._version == v
+        model.invalidate_weights()
+        h4, _ = model.infer(pts, labels=None)
+        assert torch.allclose(h4, h0 + 0.125, atol=1e-6), "invalidate_weights() did not re-upload"
+        bias.data.copy_(bias.data - 0.125)
+        model.invalidate_weights()
+        h5, _ = model.infer(pts, labels=None)
+        assert torch.allclose(h5, h0, atol=1e-6)
 
 
 def test_infer_argument_validation(cuda):
