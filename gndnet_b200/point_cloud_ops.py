@@ -4,10 +4,12 @@ Same signature, same outputs (utils/point_cloud_ops.py:107-167): ``voxels [M, ma
 (points.dtype), ``coordinates [M, 3]`` int32 (zyx when ``reverse_index``), ``num_points_per_voxel [M]``
 int32 -- bit-identical to the numba loop, including ``max_points`` truncation and the ``max_voxels``
 ``break``.  numpy in -> numpy out (like the reference); CUDA tensor in -> CUDA tensors out.
-Does not mutate ``points``.  float32 only: the reference computes in ``points.dtype`` and the
-contract for this build is float32 input.
+Does not mutate ``points``.  The kernels compute in float32; the reference computes in ``points.dtype``, so
+float64 arrays (predict_ground.py:129-131 makes one for short .npy files) are cast with a warning and the
+pillars come back as float64 ("cast-and-warn or reject").
 """
 import ctypes
+import warnings
 
 import numpy as np
 import torch
@@ -72,12 +74,19 @@ def points_to_voxel(points, voxel_size, coors_range, max_points=35, reverse_inde
     """utils/point_cloud_ops.py:107-167, same arguments and return values."""
     is_np = isinstance(points, np.ndarray)
     if is_np:
-        if points.dtype != np.float32:
-            raise TypeError("points_to_voxel: float32 points only (got %s); the reference would compute "
-                            "in that dtype" % points.dtype)
         if points.ndim != 2 or points.shape[1] < 3:
             raise ValueError("points must be [N, >=3]")
-        t = torch.from_numpy(np.ascontiguousarray(points)).cuda()
+        src_dtype = points.dtype
+        if src_dtype == np.float64:
+            # The reference computes in points.dtype (:138-141), and predict_ground.py:129-131 itself builds a float64
+            # array when a .npy file has too few columns.  The kernels are float32: cast, say so, and hand the pillars
+            # back in the caller's dtype.  A point within one float32 ulp of a cell edge may land in the neighbouring
+            # cell compared with a float64 run.
+            warnings.warn("gndnet_b200.points_to_voxel: float64 points are voxelized in float32 (the reference would "
+                          "compute in float64); pass float32 to silence this", stacklevel=2)
+        elif src_dtype != np.float32:
+            raise TypeError("points_to_voxel: float32 (or float64, cast with a warning) points only, got %s" % src_dtype)
+        t = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float32)).cuda()
     elif isinstance(points, torch.Tensor):
         if not points.is_cuda:
             raise TypeError("points_to_voxel: torch input must be a CUDA tensor (there is no CPU path)")
@@ -93,5 +102,5 @@ def points_to_voxel(points, voxel_size, coors_range, max_points=35, reverse_inde
     coors = out["coors"][0, :m]
     num = out["num_points"][0, :m]
     if is_np:
-        return voxels.cpu().numpy(), coors.cpu().numpy(), num.cpu().numpy()
+        return voxels.cpu().numpy().astype(src_dtype, copy=False), coors.cpu().numpy(), num.cpu().numpy()
     return voxels, coors, num

@@ -1,6 +1,6 @@
 """Deterministic synthetic workload: the scans (SURVEY.md section 8d recipes) and the seeded synthetic
 checkpoint that bench.py, tools/, the tests and the oracle harness all feed to BOTH sides.  Pure numpy input
-generation -- no compute of the hot path lives here (oracle/synth.py re-exports this module).
+generation -- no compute of the hot path lives here.
 
 Everything here is bit-reproducible across machines: only numpy's PCG64
 ``Generator.random`` (integer -> double conversion) and correctly-rounded

@@ -35,6 +35,22 @@ def test_points_to_voxel_dropin_bit_exact(name, cuda):
     assert synth.digest(n) == gold["num_points_digest"]
 
 
+def test_points_to_voxel_float64_is_cast_with_a_warning(cuda):
+    """predict_ground.py:129-131 builds a float64 cloud for short .npy files and the reference then computes in float64;
+    here such a cloud is voxelized in float32, loudly, and the pillars come back in the caller's dtype."""
+    from gndnet_b200.point_cloud_ops import points_to_voxel
+    cfg, raw, _ = cases.load_case("small_kitti")
+    pts = _shifted(cfg, raw)
+    v32, c32, n32 = points_to_voxel(pts, cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+    with pytest.warns(UserWarning, match="float64"):
+        v64, c64, n64 = points_to_voxel(pts.astype(np.float64), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True,
+                                        cfg.max_voxels)
+    assert v64.dtype == np.float64 and np.array_equal(v64, v32.astype(np.float64))
+    assert c64.tobytes() == c32.tobytes() and n64.tobytes() == n32.tobytes()
+    with pytest.raises(TypeError):
+        points_to_voxel(pts.astype(np.float16), cfg.voxel_size, cfg.pc_range, cfg.max_points_voxel, True, cfg.max_voxels)
+
+
 @pytest.mark.parametrize("name", ["small_kitti", "boundary_kitti"])
 def test_points_to_voxel_non_reversed(name, cuda):
     from gndnet_b200.point_cloud_ops import points_to_voxel
