@@ -249,6 +249,57 @@ def cpu_baseline(seconds, gpu_model=None, device=None, warm=2, pool=16):
     return res, parity
 
 
+def other_configs(dev, precision, B=64, steps=10, warm=4):
+    """BASELINE.json configs[3] (dense 1 M-point camera frames) and configs[4] (kittiSem with max_voxels = 1000, the
+    voxelizer's overflow break) at batch `B` on this GPU, inputs resident, the same measurement as tools/sweep.py in a
+    few steps: scans/s and the stage split of gnd_infer.  Parity of both shapes is the GPU suite's business
+    (tests/test_model_gpu.py: camera_1m and overflow_1000 / overflow_5000 through forward() and infer())."""
+    import torch
+    from gndnet_b200 import synth
+    from gndnet_b200.model import GroundEstimatorNet
+    out = {}
+    for key, cfgname, ov, gen, npool in (("configs[3] camera 1M-point frames", "camera", {}, synth.camera_scan, 2),
+                                         ("configs[4] kittiSem max_voxels=1000 (overflow)", "kitti", dict(max_voxels=1000), synth.hdl64_scan, 8)):
+        try:
+            cfg = synth.make_cfg(cfgname, **ov)
+            sd, _ = synth.checkpoint(cfgname)
+            pool = [gen(7000 + s_)[:, :cfg.input_features].copy() for s_ in range(npool)]
+            model = GroundEstimatorNet(cfg, precision=precision)
+            model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
+            model = model.to(dev).eval()
+            dpool = [torch.from_numpy(p_).to(dev) for p_ in pool]
+            pts = [torch.stack([dpool[(j + s_) % npool] for s_ in range(B)]) for j in range(2)]
+            N = pts[0].shape[1]
+            h = torch.empty((B, model.ny, model.nx), dtype=torch.float32, device=dev)
+            l = torch.empty((B, N), dtype=torch.int8, device=dev)
+            with torch.no_grad():
+                for i in range(warm):
+                    model.infer(pts[i & 1], threshold=0.08, out=(h, l))
+                torch.cuda.synchronize()
+                model.conv_timing_begin(steps)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(steps):
+                    model.infer(pts[i & 1], threshold=0.08, out=(h, l))
+                e1.record()
+                torch.cuda.synchronize()
+                conv, seg, stg = model.conv_timing_end(stages=True)
+            ms = e0.elapsed_time(e1) / steps
+            sm = stg.mean(axis=0)
+            out[key] = {"batch": B, "points_per_scan": int(N), "steps": steps, "ms_per_step": ms, "scans_per_s": B / ms * 1e3,
+                        "pillars_per_scan": float(model.pillars(B)["voxel_count"].float().mean().item()),
+                        "stage_ms": {"voxelize": float(sm[0]), "pfn_scatter": float(sm[1]), "segnet": float(sm[2]),
+                                     "segnet_convs": float(conv.sum(axis=1).mean()), "segment": float(sm[3])},
+                        "voxelize_algorithmic_gbs": B * N * 12.0 / 1e6 / float(sm[0]),
+                        "l2": "two distinct batches rotated every step (%d MB each)" % (B * N * cfg.input_features * 4 // 1000000)}
+            model.release()
+            del model, pts, dpool, h, l
+            torch.cuda.empty_cache()
+        except Exception as ex:               # a side measurement must never take the bench line down
+            out[key] = {"unavailable": repr(ex)[:200]}
+    return out
+
+
 def torch_cuda_baseline(device, gpu_model, resident, seconds=2.0):
     """The reference's GPU path as side baselines (north_star: "the reference's PyTorch CUDA forward on the same GPUs").
     (1) its deployment shape, batch 1 (ros_node.py:61-66, 96-126): CPU voxelization -> pageable H2D of the dense
@@ -777,6 +828,8 @@ def main():
                     del m2
                 except Exception as ex:
                     extra["precision_split"] = {"unavailable": repr(ex)[:200]}
+            if world == 1 and B == 64:
+                extra["configs"] = other_configs(dev, args.precision)
             if not args.no_cpu_baseline:
                 extra["cpu_baseline"], extra["parity"] = cpu_baseline(args.cpu_seconds, gpu_model=model, device=dev)
                 try:
@@ -822,7 +875,7 @@ def main():
         if lat:
             line["e2e"]["latency"] = lat
         if isinstance(line.get("roofline"), dict):
-            for k in ("hbm_stages", "stage_ms", "precision_split", "value_direct_launches"):
+            for k in ("hbm_stages", "stage_ms", "precision_split", "value_direct_launches", "configs"):
                 if k in extra:
                     line["roofline"][k] = extra[k]
         if isinstance(line.get("cpu_baseline"), dict):
